@@ -1,0 +1,2 @@
+#pragma once
+#include "upcxx_utils.hpp"
