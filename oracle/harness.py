@@ -1,0 +1,177 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes front end to the two CPU checkers.
+
+* ``port``: oracle/libkcount_oracle.so, the plain-C restatement (kcount_oracle.c), always buildable.
+* ``ref`` : oracle/_ref/libkcount_ref.so, the reference's own kcount_cpu.cpp/kmer_dht.cpp/kmer.cpp/hash_funcs.c compiled
+  unmodified from /root/reference (ref_driver.cpp); built in the authoring container, travels to the GPU box prebuilt.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this module.
+The product package (mhm2_proxy_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+PORT_SO = os.path.join(HERE, "libkcount_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libkcount_ref.so")
+
+
+def build(verbose=False):
+    """Compile the C restatement and, when /root/reference is present, the reference build."""
+    out = subprocess.run(["make", "-C", HERE, "all"], capture_output=True, text=True)
+    if verbose or out.returncode:
+        print(out.stdout[-2000:], out.stderr[-4000:])
+    if out.returncode:
+        raise RuntimeError("oracle build failed")
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+_libs = {}
+
+
+def _lib(kind):
+    if kind in _libs:
+        return _libs[kind]
+    path, pfx = (PORT_SO, "ko_") if kind == "port" else (REF_SO, "oref_")
+    if not os.path.exists(path):
+        if kind == "port":
+            build()
+        else:
+            raise FileNotFoundError(path)
+    lib = C.CDLL(path)
+    f = lambda n: getattr(lib, pfx + n)
+    run = f("run")
+    run.restype = C.c_void_p
+    common = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+    run.argtypes = common + ([C.c_int] if kind == "port" else [C.c_double, C.c_uint64, C.c_int])
+    f("n_longs").argtypes = [C.c_void_p]
+    f("n_longs").restype = C.c_int
+    for n in ("num_survivors", "num_prefilter"):
+        f(n).argtypes = [C.c_void_p]
+        f(n).restype = C.c_uint64
+    f("copy_survivors").argtypes = [C.c_void_p] * 6
+    f("copy_prefilter").argtypes = [C.c_void_p] * 3
+    f("stats").argtypes = [C.c_void_p] * 3
+    f("free").argtypes = [C.c_void_p]
+    f("kmer_prims").argtypes = [C.c_int, C.c_char_p, C.c_int] + [C.c_void_p] * 6
+    f("kmer_prims").restype = C.c_int
+    f("murmur64").argtypes = [C.c_void_p, C.c_uint32]
+    f("murmur64").restype = C.c_uint64
+    f("quick_hash").argtypes = [C.c_uint64]
+    f("quick_hash").restype = C.c_uint64
+    g = f("get_ext4") if kind == "port" else f("get_ext")
+    g.argtypes = [C.c_uint16] * 5 + [C.c_int]
+    g.restype = C.c_char
+    _libs[kind] = (lib, pfx)
+    return _libs[kind]
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class OracleResult:
+    """Survivors sorted by key words; prefilter rows (after the reads pass) sorted by key words too."""
+
+    def __init__(self):
+        self.n_longs = 0
+        self.keys = self.counts = self.left = self.right = self.shard = None
+        self.pf_keys = self.pf_vals = None
+        self.stats = {}
+        self.times = (0.0, 0.0, 0.0)
+
+
+def run(kind, k, read_bytes, read_offsets, dmin_thres=2, num_shards=1, qual_offset=33, ctg_seqs=None, ctg_offsets=None,
+        ctg_depths=None, want_prefilter=False, free_mem=None, num_elems=None):
+    """Run kcount on the CPU. read_bytes: uint8 PackedRead bytes; read_offsets: uint64[n+1]."""
+    lib, pfx = _lib(kind)
+    f = lambda n: getattr(lib, pfx + n)
+    rb = np.ascontiguousarray(read_bytes, dtype=np.uint8)
+    ro = np.ascontiguousarray(read_offsets, dtype=np.uint64)
+    n_reads = len(ro) - 1
+    n_ctgs = 0
+    cs = co = cd = None
+    if ctg_offsets is not None and len(ctg_offsets) > 1:
+        cs = np.ascontiguousarray(ctg_seqs, dtype=np.uint8)
+        co = np.ascontiguousarray(ctg_offsets, dtype=np.uint64)
+        cd = np.ascontiguousarray(ctg_depths, dtype=np.float64)
+        n_ctgs = len(co) - 1
+    args = [k, qual_offset, dmin_thres, num_shards, _p(rb), _p(ro), n_reads, _p(cs), _p(co), _p(cd), n_ctgs]
+    if kind == "port":
+        args.append(int(want_prefilter))
+    else:
+        lens = np.diff(ro.astype(np.int64))
+        inst = int(np.maximum(lens - k - 1, 0).sum())
+        if n_ctgs:
+            inst += int(np.maximum(np.diff(co.astype(np.int64)) - k - 1, 0).sum())
+        ne = int(num_elems if num_elems is not None else max(inst, 1000))
+        w = 8 * (k // 32 + 1)
+        # capacity = min(0.6*free/(W+20), 3*num_elems) (kcount_cpu.cpp:431-438): make memory non-binding by default
+        fm = float(free_mem if free_mem is not None else 3.2 * ne * (w + 20) / 0.6)
+        args += [fm, ne, int(want_prefilter)]
+    h = f("run")(*args)
+    if not h:
+        raise RuntimeError(f"oracle {kind} run failed")
+    try:
+        res = OracleResult()
+        nl = res.n_longs = f("n_longs")(h)
+        n = f("num_survivors")(h)
+        res.keys = np.zeros((n, nl), dtype=np.uint64)
+        res.counts = np.zeros(n, dtype=np.uint16)
+        res.left = np.zeros(n, dtype=np.uint8)
+        res.right = np.zeros(n, dtype=np.uint8)
+        res.shard = np.zeros(n, dtype=np.int32)
+        f("copy_survivors")(h, _p(res.keys), _p(res.counts), _p(res.left), _p(res.right), _p(res.shard))
+        if want_prefilter:
+            npf = f("num_prefilter")(h)
+            pk = np.zeros((npf, nl), dtype=np.uint64)
+            pv = np.zeros((npf, 9), dtype=np.uint16)
+            f("copy_prefilter")(h, _p(pk), _p(pv))
+            order = np.lexsort([pk[:, j] for j in range(nl - 1, -1, -1)])
+            res.pf_keys, res.pf_vals = pk[order], pv[order]
+        st = np.zeros(8, dtype=np.uint64)
+        tm = np.zeros(3, dtype=np.float64)
+        f("stats")(h, _p(st), _p(tm))
+        names = ["instances", "distinct_after_reads", "dropped", "singleton_overrides", "supermers", "supermer_bytes",
+                 "ctg_instances", "purged"]
+        res.stats = {nm: int(v) for nm, v in zip(names, st)}
+        res.times = tuple(float(x) for x in tm)
+        return res
+    finally:
+        f("free")(h)
+
+
+def kmer_prims(kind, kmer_str, num_shards=1):
+    """(words, rc_words, minimizer, slot_hash, owner, m) of an ASCII k-mer."""
+    lib, pfx = _lib(kind)
+    k = len(kmer_str)
+    w = np.zeros(4, dtype=np.uint64)
+    r = np.zeros(4, dtype=np.uint64)
+    mn = np.zeros(1, dtype=np.uint64)
+    hs = np.zeros(1, dtype=np.uint64)
+    ow = np.zeros(1, dtype=np.int32)
+    m = np.zeros(1, dtype=np.int32)
+    nl = getattr(lib, pfx + "kmer_prims")(k, kmer_str.encode(), num_shards, _p(w), _p(r), _p(mn), _p(hs), _p(ow), _p(m))
+    return w[:nl].copy(), r[:nl].copy(), int(mn[0]), int(hs[0]), int(ow[0]), int(m[0])
+
+
+def murmur64(kind, words):
+    lib, pfx = _lib(kind)
+    a = np.ascontiguousarray(words, dtype=np.uint64)
+    return int(getattr(lib, pfx + "murmur64")(_p(a), a.size * 8))
+
+
+def quick_hash(kind, v):
+    lib, pfx = _lib(kind)
+    return int(getattr(lib, pfx + "quick_hash")(int(v)))
+
+
+def get_ext(kind, a, c, g, t, count, dmin_thres=2):
+    lib, pfx = _lib(kind)
+    fn = getattr(lib, pfx + ("get_ext4" if kind == "port" else "get_ext"))
+    return fn(a, c, g, t, count, dmin_thres).decode()

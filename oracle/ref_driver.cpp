@@ -38,6 +38,12 @@
 #include "kcount/kmer_dht.cpp"
 #include "kcount/kcount_cpu.cpp"
 
+// what cmake generates from extern_template.in.cpp for kmer (src/CMakeLists.txt): one explicit instantiation per MAX_K
+__MACRO_KMER__(32, template);
+__MACRO_KMER__(64, template);
+__MACRO_KMER__(96, template);
+__MACRO_KMER__(128, template);
+
 // free functions the reference declares in utils.hpp and defines in utils.cpp (not compiled here: utils.cpp drags
 // in the whole option/pinning layer). Restated from utils.cpp:71-75 and utils.cpp:121-143.
 size_t estimate_hashtable_memory(size_t num_elements, size_t element_size) {
