@@ -1,0 +1,126 @@
+/* kcount_b200.h — C ABI of the B200-native kcount (k-mer analysis) hot path of MetaHipMer2.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types, int status codes (0 = ok), no
+ * exceptions. Every entry point names the reference interface it replaces (paths relative to the reference's src/).
+ * The reference-side binding (kcount_b200.cpp implementing SeqBlockInserter<MAX_K>/HashTableInserter<MAX_K>) is in
+ * INTEGRATION.md and mhm2_proxy_b200/csrc/kcount_b200_host.hpp.
+ *
+ * Semantics = the reference CPU path (kcount/kcount_cpu.cpp), bit-exact: canonical k-mer, saturating u16 count,
+ * chosen left/right extension char (A,C,G,T,F,X); 'N' packs as 'G' in k-mers and never counts as an extension; first
+ * and last k-mer of every sequence are not counted. See DESIGN.md.
+ */
+#ifndef KCOUNT_B200_H
+#define KCOUNT_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KC_OK 0
+#define KC_ERR_INVALID 1   /* bad argument / configuration */
+#define KC_ERR_CUDA 2      /* CUDA runtime error; text in kc_last_error */
+#define KC_ERR_STATE 3     /* call out of order (e.g. add after finish) */
+#define KC_ERR_NOMEM 4     /* device or host allocation failed */
+#define KC_ERR_BADCHAR 5   /* contig character outside ACGTNacgtn (reference DIEs: kcount_cpu.cpp:455-459) */
+#define KC_ERR_COMM 6      /* NCCL error */
+#define KC_ERR_OVERFLOW 7  /* survivor output capacity exceeded (reported, never silent) */
+
+typedef struct kc_handle kc_handle;
+
+/* Values of the reference's run-time options and compile-time constants that parameterise the path
+ * (options.cpp:260-304, CMakeDefinitions.txt:46-63). Zero-initialise, then call kc_config_default(). */
+typedef struct kc_config {
+  int32_t kmer_len;          /* k, 1..127; N_LONGS = k/32 + 1 words per key as in main.cpp:170 / kmer.hpp:64 */
+  int32_t qual_cutoff;       /* KCOUNT_QUAL_CUTOFF = 20: packed quality below this => base is low quality */
+  int32_t dmin_thres;        /* --min-depth-thres, default 2 (options.hpp:96); must be >= 1 */
+  double dyn_min_depth;      /* DYN_MIN_DEPTH = 0.9 (kcount_cpu.cpp:178) */
+  int32_t num_shards;        /* = upcxx::rank_n(): table is sharded by quick_hash(minimizer) % num_shards */
+  int32_t shard_id;          /* = upcxx::rank_me(): which shard this handle owns */
+  int32_t device;            /* CUDA device ordinal (reference: rank % ndev, gpu_utils.cpp:68-75) */
+  int32_t num_partitions;    /* 0 = auto. Power of two. L2-sized sub-tables per shard (internal, result-invariant) */
+  uint64_t expected_instances; /* hint: total k-mer instances this shard's caller will add (0 = size from first add);
+                                  plays the role of estimate_num_kmers (contigging.cpp:61-91) */
+  int32_t keep_prefilter;    /* 1 = also keep every distinct k-mer's counters after the reads pass (debug parity) */
+  int32_t batch_reads;       /* 0 = auto. reads per internal batch (H2D copy / parse / exchange pipelining unit) */
+  int32_t l2_table_mb;       /* 0 = auto. budget for the group of partition tables processed together */
+  int32_t reserved[5];
+} kc_config;
+
+/* counters the reference logs (kcount.cpp:93-97, kcount_cpu.cpp:107-112,467-487,525-527) */
+typedef struct kc_stats {
+  uint64_t num_seqs;            /* reads + contigs added through this handle */
+  uint64_t num_bases;
+  uint64_t instances_parsed;    /* k-mer instances parsed locally: sum max(0, len-k-1) */
+  uint64_t instances_inserted;  /* k-mer instances inserted into this shard's table (reads + contigs) */
+  uint64_t ctg_instances_inserted;
+  uint64_t supermers_out;       /* supermers produced locally */
+  uint64_t supermer_bytes_out;  /* bytes of packed supermers produced locally */
+  uint64_t supermer_bytes_sent; /* of those, bytes that left this GPU */
+  uint64_t supermers_in;        /* supermers inserted here */
+  uint64_t distinct;            /* distinct canonical k-mers in this shard before the filter */
+  uint64_t purged;              /* distinct - survivors */
+  uint64_t survivors;
+  uint64_t dropped;             /* always 0: partition tables are re-run larger instead of dropping */
+  uint64_t table_retries;       /* partitions re-run with a larger table */
+  uint64_t max_probe;
+  uint64_t num_partitions;
+  double ms_h2d, ms_parse, ms_exchange, ms_insert, ms_filter, ms_total; /* CUDA-event times, this handle */
+  uint64_t gpu_launches;        /* kernels launched by this handle so far */
+  uint64_t reserved[8];
+} kc_stats;
+
+void kc_config_default(kc_config *cfg, int32_t kmer_len);
+
+/* KmerDHT<MAX_K> ctor + HashTableInserter<MAX_K>::init (kmer_dht.cpp:105-154, kcount_cpu.cpp:425-443) */
+int kc_create(const kc_config *cfg, kc_handle **out);
+/* ~KmerDHT / ~HashTableInserter (kmer_dht.cpp:161-166, kcount_cpu.cpp:417-423) */
+int kc_destroy(kc_handle *h);
+const char *kc_last_error(const kc_handle *h);
+
+/* count_kmers' read loop -> SeqBlockInserter::process_seq(seq, 0) (kcount.cpp:72-88, kcount_cpu.cpp:73-103).
+ * bytes = PackedRead bytes verbatim (packed_reads.cpp:73-109: base 0..4 | min(qual,31) << 3), offsets[n_reads+1].
+ * HOST pointers (pinned memory copies faster); the caller keeps ownership; returns when the data has been consumed. */
+int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *offsets, uint64_t n_reads);
+/* same, DEVICE pointers already resident on cfg.device (no copy). total_bytes = offsets[n_reads]. */
+int kc_add_reads_device(kc_handle *h, const uint8_t *d_bytes, const uint64_t *d_offsets, uint64_t n_reads, uint64_t total_bytes,
+                        uint32_t max_read_len);
+/* add_ctg_kmers' loop -> process_seq(ctg.seq, ctg.get_uint16_t_depth()) (kcount.cpp:123-130, contigs.hpp:57-66).
+ * seqs = ASCII ACGTN (host), offsets[n+1], depths = Contig::depth doubles. Any length; long contigs are tiled. */
+int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs);
+
+/* multi-GPU: bind an NCCL communicator built from a 128-byte ncclUniqueId shared by all shards
+ * (replaces ThreeTierAggrStore<Supermer> / rpc_ff, kmer_dht.cpp:133,146-149,222-231). Not needed when num_shards==1. */
+int kc_comm_unique_id(uint8_t id128[128]);
+int kc_comm_init(kc_handle *h, const uint8_t id128[128]);
+
+/* KmerDHT::flush_updates + finish_updates -> HashTableInserter::insert_into_local_hashtable
+ * (kmer_dht.cpp:227-236, kcount_cpu.cpp:490-528). Collective across shards when num_shards > 1. */
+int kc_finish(kc_handle *h);
+
+/* local_kmers of this shard (kmer_dht.hpp:119, dbjg_traversal.cpp:301): n rows of N_LONGS words, u16 count, left, right */
+int kc_num_survivors(kc_handle *h, uint64_t *n);
+int kc_copy_survivors(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char *left, char *right);
+/* device-resident view of the same arrays (valid until kc_destroy) */
+int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,
+                        const char **d_right);
+/* pre-filter counters after the reads pass (KmerMapExts contents, kcount_cpu.cpp:191-200): vals = n x 9 u16
+ * {count, left A,C,G,T, right A,C,G,T}, saturated at 65535. Needs cfg.keep_prefilter. */
+int kc_num_prefilter(kc_handle *h, uint64_t *n);
+int kc_copy_prefilter(kc_handle *h, uint64_t *kmer_words, uint16_t *vals9);
+
+int kc_get_stats(kc_handle *h, kc_stats *st);
+
+/* ---- primitives, exported for known-answer tests of the device code (each runs a tiny kernel) ----
+ * kmers: n ASCII k-mers of length k back to back. Outputs per k-mer: words[N_LONGS], rc_words[N_LONGS],
+ * minimizer (kmer.cpp:345-393), slot hash = MurmurHash3_x64_64 (kmer.cpp:465-468), owner = quick_hash(minimizer) %
+ * num_shards (kmer_dht.cpp:192-196). */
+int kc_prim_kmers(int32_t device, int32_t k, const char *kmers, uint64_t n, int32_t num_shards, uint64_t *words, uint64_t *rc_words,
+                  uint64_t *minimizer, uint64_t *hash, int32_t *owner);
+/* ExtCounts::get_ext (kcount_cpu.cpp:173-182) for n rows of {A,C,G,T,count} u16 */
+int kc_prim_get_ext(int32_t device, const uint16_t *acgt_count5, uint64_t n, int32_t dmin_thres, double dyn_min_depth, char *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,947 @@
+// Host side of the B200 kcount library and its C ABI (include/kcount_b200.h).
+// One handle = one shard (one GPU). Pipeline per handle:
+//   add_reads/add_contigs : [H2D copy] -> parse COUNT -> exact bucket layout -> parse FILL          (kc_parse.cuh)
+//   finish                : [NCCL all-to-all of the per-shard bucket ranges] -> per group of partitions:
+//                           clear tables -> insert -> filter/compact                               (kc_count.cuh)
+// There is no CPU fallback: every data-path step is a CUDA kernel; host code only sizes, allocates and launches.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <dlfcn.h>
+
+#include "../../include/kcount_b200.h"
+#include "kc_count.cuh"
+#include "kc_parse.cuh"
+
+using namespace kc;
+
+namespace {
+
+constexpr int SEG_MAX = 1024;  // longest sequence a parse warp handles in one piece; longer ones are tiled with k+1 overlap
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+};
+
+// one parsed batch (or one received batch): supermers of every bucket laid out bucket-major
+struct Block {
+  SupHdr *hdr = nullptr;
+  u32 *payload = nullptr;
+  std::vector<BucketHist> hist;  // per bucket of the PRODUCER (num_shards*P) for local blocks; P entries for received
+  std::vector<u64> hdr_base, pay_base;
+  u64 tot_sup = 0, tot_words = 0;
+  bool is_ctg = false;
+  bool received = false;  // true: indexed by partition only
+};
+
+struct Nccl;  // opaque, kc_comm.inl
+
+}  // namespace
+
+struct kc_handle {
+  kc_config cfg;
+  int KW = 1, m = 15, w = 1;
+  u32 P = 0;  // partitions per shard (0 until the first add decides)
+  bool finished = false, has_ctg = false;
+  cudaStream_t s_main = nullptr, s_copy = nullptr;
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
+  std::vector<Block> blocks;       // produced locally
+  std::vector<Block> rblocks;      // received from peers (multi-shard)
+  DevBuf stage_bytes[2], stage_offs[2];
+  DevBuf d_hist, d_cursor, d_hdr_base, d_pay_base, d_misc;  // d_misc: u64 instances, u32 err
+  // outputs
+  DevBuf out_keys, out_counts, out_left, out_right, pf_keys, pf_vals;
+  u64 n_surv = 0, n_pf = 0;
+  kc_stats st;
+  std::string err;
+  Nccl *comm = nullptr;
+};
+
+namespace {
+
+int fail(kc_handle *h, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf;
+  return code;
+}
+
+#define CK(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess)                                                                               \
+      return fail(h, e_ == cudaErrorMemoryAllocation ? KC_ERR_NOMEM : KC_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                  cudaGetErrorString(e_));                                                               \
+  } while (0)
+
+#define RC(call)            \
+  do {                      \
+    int r_ = (call);        \
+    if (r_) return r_;      \
+  } while (0)
+
+int ensure(kc_handle *h, DevBuf &b, size_t bytes) {
+  if (b.bytes >= bytes && b.p) return KC_OK;
+  if (b.p) CK(cudaFree(b.p));
+  b.p = nullptr;
+  b.bytes = 0;
+  size_t want = bytes + bytes / 8 + 256;
+  CK(cudaMalloc(&b.p, want));
+  b.bytes = want;
+  return KC_OK;
+}
+
+void release(DevBuf &b) {
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.bytes = 0;
+}
+
+u32 next_pow2(u64 v) {
+  u64 p = 1;
+  while (p < v) p <<= 1;
+  return (u32)std::min<u64>(p, 1ull << 31);
+}
+
+float elapsed(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0;
+  cudaEventElapsedTime(&ms, a, b);
+  return ms;
+}
+
+}  // namespace
+
+extern "C" void kc_config_default(kc_config *cfg, int32_t kmer_len) {
+  memset(cfg, 0, sizeof(*cfg));
+  cfg->kmer_len = kmer_len;
+  cfg->qual_cutoff = 20;     // KCOUNT_QUAL_CUTOFF, CMakeDefinitions.txt:46
+  cfg->dmin_thres = 2;       // options.hpp:96
+  cfg->dyn_min_depth = 0.9;  // DYN_MIN_DEPTH, CMakeDefinitions.txt:60
+  cfg->num_shards = 1;
+  cfg->shard_id = 0;
+  cfg->device = 0;
+}
+
+extern "C" const char *kc_last_error(const kc_handle *h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
+  if (!cfg || !out) return KC_ERR_INVALID;
+  *out = nullptr;
+  kc_handle *h = new kc_handle();
+  h->cfg = *cfg;
+  memset(&h->st, 0, sizeof(h->st));
+  *out = h;  // returned even on failure so that kc_last_error can be read; caller destroys it
+  const int k = cfg->kmer_len;
+  if (k < 2 || k > 127) return fail(h, KC_ERR_INVALID, "kmer_len %d outside 2..127", k);
+  if (cfg->dmin_thres < 1) return fail(h, KC_ERR_INVALID, "dmin_thres must be >= 1");
+  if (cfg->num_shards < 1 || cfg->shard_id < 0 || cfg->shard_id >= cfg->num_shards)
+    return fail(h, KC_ERR_INVALID, "bad shard %d of %d", cfg->shard_id, cfg->num_shards);
+  if (cfg->num_partitions && (cfg->num_partitions & (cfg->num_partitions - 1)))
+    return fail(h, KC_ERR_INVALID, "num_partitions must be a power of two");
+  h->KW = k / 32 + 1;  // main.cpp:170, kmer.hpp:64
+  int m = k * 2 / 3 + 1;  // kmer_dht.cpp:113-116
+  if (m < 15) m = 15;
+  if (m > 27) m = 27;
+  if (m > k) m = k;  // reference asserts m <= k (kmer.cpp:346); only reachable for k < 15
+  h->m = m;
+  h->w = k - m + 1;
+  int ndev = 0;
+  CK(cudaGetDeviceCount(&ndev));
+  if (cfg->device < 0 || cfg->device >= ndev) return fail(h, KC_ERR_INVALID, "device %d of %d", cfg->device, ndev);
+  CK(cudaSetDevice(cfg->device));
+  CK(cudaStreamCreateWithFlags(&h->s_main, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&h->ev_a));
+  CK(cudaEventCreate(&h->ev_b));
+  for (int i = 0; i < 2; i++) {
+    CK(cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
+  }
+  RC(ensure(h, h->d_misc, 64));
+  CK(cudaMemsetAsync(h->d_misc.p, 0, 64, h->s_main));
+  return KC_OK;
+}
+
+namespace {
+
+void decide_partitions(kc_handle *h, u64 inst_estimate) {
+  if (h->P) return;
+  if (h->cfg.num_partitions) {
+    h->P = (u32)h->cfg.num_partitions;
+  } else {
+    u64 est = h->cfg.expected_instances ? h->cfg.expected_instances : inst_estimate;
+    // ~512K instances per partition keeps a partition's table (tens of thousands to ~100K distinct keys) at a few MB,
+    // so that a group of them is resident in the 126 MB L2 while it is being built
+    u64 want = (est + (512u << 10) - 1) / (512u << 10);
+    u32 p = next_pow2(std::max<u64>(want, 1));
+    h->P = std::min<u32>(p, 8192u);
+  }
+  while ((u64)h->P * (u64)h->cfg.num_shards > 65536ull) h->P >>= 1;  // bucket ids are u16 inside the parse kernel
+  h->st.num_partitions = h->P;
+}
+
+// Parse one batch that is already on the device. `bytes` may be a virtual base (bytes + start always lands inside
+// the staged range). Either offsets (direct mode) or seg_* (segment mode) is given.
+int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, const u64 *d_seg_start, const u32 *d_seg_len,
+                const uint16_t *d_seg_depth, u64 nseq, int max_len, bool ascii, bool is_ctg) {
+  if (nseq == 0) return KC_OK;
+  const u32 NP = h->P * (u32)h->cfg.num_shards;
+  RC(ensure(h, h->d_hist, sizeof(BucketHist) * NP));
+  RC(ensure(h, h->d_cursor, sizeof(BucketHist) * NP));
+  RC(ensure(h, h->d_hdr_base, sizeof(u64) * NP));
+  RC(ensure(h, h->d_pay_base, sizeof(u64) * NP));
+  ParseArgs a;
+  memset(&a, 0, sizeof(a));
+  a.bytes = d_bytes;
+  a.offsets = d_offsets;
+  a.seg_start = d_seg_start;
+  a.seg_len = d_seg_len;
+  a.seg_depth = d_seg_depth;
+  a.nseq = nseq;
+  a.ascii = ascii ? 1 : 0;
+  a.k = h->cfg.kmer_len;
+  a.m = h->m;
+  a.w = h->w;
+  a.qual_cutoff = h->cfg.qual_cutoff;
+  a.num_shards = (u32)h->cfg.num_shards;
+  a.num_parts = h->P;
+  a.max_len = (std::max(max_len, 32) + 31) & ~31;
+  a.nsb = a.max_len / 16 + 4;
+  a.nsv = a.max_len / 32 + 2;
+  a.smem_per_warp = (a.max_len * 8 + (a.nsb + 2 * a.nsv) * 4 + a.max_len * 2 + 15) & ~15;
+  a.instances = (u64 *)h->d_misc.p;
+  a.err = (u32 *)((char *)h->d_misc.p + 8);
+  int warps = PARSE_THREADS / 32;
+  while (warps > 1 && (size_t)warps * a.smem_per_warp > 200u * 1024u) warps >>= 1;
+  const size_t smem = (size_t)warps * a.smem_per_warp;
+  if (smem > 220u * 1024u) return fail(h, KC_ERR_INVALID, "sequence too long for one parse warp: %d", max_len);
+  CK(cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CK(cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int dev_sms = 148;
+  cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->cfg.device);
+  int per_sm = 1;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, parse_kernel<true>, warps * 32, smem));
+  per_sm = std::max(per_sm, 1);
+  u64 need_blocks = (nseq + warps - 1) / warps;
+  const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)dev_sms * per_sm * 4);
+
+  cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
+  CK(cudaEventRecord(e0, h->s_main));
+  // COUNT
+  CK(cudaMemsetAsync(h->d_hist.p, 0, sizeof(BucketHist) * NP, h->s_main));
+  a.hist = (BucketHist *)h->d_hist.p;
+  parse_kernel<false><<<grid, warps * 32, smem, h->s_main>>>(a);
+  h->st.gpu_launches++;
+  CK(cudaGetLastError());
+  Block blk;
+  blk.is_ctg = is_ctg;
+  blk.hist.resize(NP);
+  CK(cudaMemcpyAsync(blk.hist.data(), h->d_hist.p, sizeof(BucketHist) * NP, cudaMemcpyDeviceToHost, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
+  blk.hdr_base.resize(NP + 1);
+  blk.pay_base.resize(NP + 1);
+  u64 hs = 0, ps = 0;
+  for (u32 b = 0; b < NP; b++) {
+    blk.hdr_base[b] = hs;
+    blk.pay_base[b] = ps;
+    hs += blk.hist[b].nsup;
+    ps += blk.hist[b].nwords;
+  }
+  blk.hdr_base[NP] = hs;
+  blk.pay_base[NP] = ps;
+  blk.tot_sup = hs;
+  blk.tot_words = ps;
+  if (hs == 0) {
+    CK(cudaEventRecord(e1, h->s_main));
+    return KC_OK;
+  }
+  CK(cudaMalloc((void **)&blk.hdr, sizeof(SupHdr) * (hs + 1)));
+  CK(cudaMalloc((void **)&blk.payload, sizeof(u32) * (ps + 8)));  // + slack: fetch64 may read 2 words past a record
+  CK(cudaMemsetAsync(blk.payload + ps, 0, sizeof(u32) * 8, h->s_main));
+  CK(cudaMemcpyAsync(h->d_hdr_base.p, blk.hdr_base.data(), sizeof(u64) * NP, cudaMemcpyHostToDevice, h->s_main));
+  CK(cudaMemcpyAsync(h->d_pay_base.p, blk.pay_base.data(), sizeof(u64) * NP, cudaMemcpyHostToDevice, h->s_main));
+  CK(cudaMemsetAsync(h->d_cursor.p, 0, sizeof(BucketHist) * NP, h->s_main));
+  // FILL
+  a.hist = (BucketHist *)h->d_cursor.p;
+  a.hdr_base = (const u64 *)h->d_hdr_base.p;
+  a.pay_base = (const u64 *)h->d_pay_base.p;
+  a.hdr = blk.hdr;
+  a.payload = blk.payload;
+  parse_kernel<true><<<grid, warps * 32, smem, h->s_main>>>(a);
+  h->st.gpu_launches++;
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(e1, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));  // hdr_base/pay_base host vectors are about to move; also surfaces kernel faults here
+  h->st.ms_parse += elapsed(e0, e1);
+  h->st.supermers_out += hs;
+  h->st.supermer_bytes_out += hs * sizeof(SupHdr) + ps * 4;
+  h->blocks.push_back(std::move(blk));
+  return KC_OK;
+}
+
+}  // namespace
+
+extern "C" int kc_add_reads_device(kc_handle *h, const uint8_t *d_bytes, const uint64_t *d_offsets, uint64_t n_reads,
+                                   uint64_t total_bytes, uint32_t max_read_len) {
+  if (!h) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "add after finish");
+  if (n_reads == 0) return KC_OK;
+  if (max_read_len > (uint32_t)SEG_MAX)
+    return fail(h, KC_ERR_INVALID, "device-resident reads longer than %d must be tiled by the caller (use kc_add_reads)", SEG_MAX);
+  CK(cudaSetDevice(h->cfg.device));
+  const u64 k1 = (u64)h->cfg.kmer_len + 1;
+  decide_partitions(h, total_bytes > n_reads * k1 ? total_bytes - n_reads * k1 : 0);
+  const u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : (8ull << 20);
+  for (u64 r0 = 0; r0 < n_reads; r0 += batch) {
+    const u64 n = std::min<u64>(batch, n_reads - r0);
+    int rc = parse_batch(h, d_bytes, (const u64 *)d_offsets + r0, nullptr, nullptr, nullptr, n, (int)max_read_len, false, false);
+    if (rc) return rc;
+  }
+  h->st.num_seqs += n_reads;
+  h->st.num_bases += total_bytes;
+  return KC_OK;
+}
+
+namespace {
+
+// Tile a sequence of `len` bases starting at absolute byte `start` into segments of at most `tile` bases that overlap by
+// k+1 bases, so that every counted k-mer position 1..len-k-1 belongs to exactly one segment (the reference GPU path
+// refuses sequences longer than its block instead: kcount_gpu.cpp:138-140).
+void tile_sequence(u64 start, u64 len, int k, int tile, uint16_t depth, std::vector<u64> &ss, std::vector<u32> &sl,
+                   std::vector<uint16_t> &sd) {
+  if (len < (u64)k + 2) return;
+  u64 s = 0;
+  for (;;) {
+    u64 l = std::min<u64>((u64)tile, len - s);
+    ss.push_back(start + s);
+    sl.push_back((u32)l);
+    sd.push_back(depth);
+    if (s + l == len) break;
+    s += l - (u64)k - 1;
+  }
+}
+
+// copy host arrays of segments to the device and parse them
+int parse_segments(kc_handle *h, const uint8_t *d_bytes_virtual, std::vector<u64> &ss, std::vector<u32> &sl, std::vector<uint16_t> &sd,
+                   int max_len, bool ascii, bool is_ctg) {
+  const u64 n = ss.size();
+  if (!n) return KC_OK;
+  DevBuf b0, b1, b2;
+  int rc = ensure(h, b0, n * 8);
+  if (!rc) rc = ensure(h, b1, n * 4);
+  if (!rc) rc = ensure(h, b2, n * 2);
+  if (!rc) {
+    cudaMemcpyAsync(b0.p, ss.data(), n * 8, cudaMemcpyHostToDevice, h->s_main);
+    cudaMemcpyAsync(b1.p, sl.data(), n * 4, cudaMemcpyHostToDevice, h->s_main);
+    cudaMemcpyAsync(b2.p, sd.data(), n * 2, cudaMemcpyHostToDevice, h->s_main);
+    rc = parse_batch(h, d_bytes_virtual, nullptr, (const u64 *)b0.p, (const u32 *)b1.p, (const uint16_t *)b2.p, n, max_len, ascii,
+                     is_ctg);
+  }
+  cudaStreamSynchronize(h->s_main);
+  release(b0);
+  release(b1);
+  release(b2);
+  return rc;
+}
+
+}  // namespace
+
+extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *offsets, uint64_t n_reads) {
+  if (!h) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "add after finish");
+  if (n_reads == 0) return KC_OK;
+  if (!bytes || !offsets) return fail(h, KC_ERR_INVALID, "null input");
+  CK(cudaSetDevice(h->cfg.device));
+  const int k = h->cfg.kmer_len;
+  u64 max_len = 0, inst = 0;
+  for (u64 r = 0; r < n_reads; r++) {
+    const u64 l = offsets[r + 1] - offsets[r];
+    max_len = std::max(max_len, l);
+    if (l >= (u64)k + 2) inst += l - k - 1;
+  }
+  decide_partitions(h, inst);
+  const bool tiled = max_len > (u64)SEG_MAX;
+  u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : (4ull << 20);
+  const u64 avg = std::max<u64>(1, (offsets[n_reads] - offsets[0]) / n_reads);
+  batch = std::max<u64>(1, std::min<u64>(batch, (1ull << 30) / avg));  // <= ~1 GB of bases per batch
+  const u64 nb = (n_reads + batch - 1) / batch;
+  cudaEvent_t t0, t1;
+  CK(cudaEventCreate(&t0));
+  CK(cudaEventCreate(&t1));
+  float ms_copy = 0;
+  auto issue_copy = [&](u64 bi) -> int {
+    const int sl = (int)(bi & 1);
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    const u64 b0 = offsets[r0], b1 = offsets[r1];
+    CK(cudaEventSynchronize(h->ev_free[sl]));  // the parse that last used this stage has finished
+    RC(ensure(h, h->stage_bytes[sl], b1 - b0 + 64));
+    RC(ensure(h, h->stage_offs[sl], (r1 - r0 + 1) * 8));
+    CK(cudaEventRecord(t0, h->s_copy));
+    CK(cudaMemcpyAsync(h->stage_bytes[sl].p, bytes + b0, b1 - b0, cudaMemcpyHostToDevice, h->s_copy));
+    CK(cudaMemcpyAsync(h->stage_offs[sl].p, offsets + r0, (r1 - r0 + 1) * 8, cudaMemcpyHostToDevice, h->s_copy));
+    CK(cudaEventRecord(t1, h->s_copy));
+    CK(cudaEventRecord(h->ev_copy[sl], h->s_copy));
+    h->st.supermer_bytes_sent += 0;
+    return KC_OK;
+  };
+  int rc = issue_copy(0);
+  if (rc) return rc;
+  for (u64 bi = 0; bi < nb; bi++) {
+    const int sl = (int)(bi & 1);
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    CK(cudaEventSynchronize(h->ev_copy[sl]));
+    ms_copy += elapsed(t0, t1);
+    if (bi + 1 < nb) {  // next batch's copy overlaps this batch's parse
+      rc = issue_copy(bi + 1);
+      if (rc) return rc;
+    }
+    const uint8_t *vbase = (const uint8_t *)h->stage_bytes[sl].p - offsets[r0];
+    if (!tiled) {
+      rc = parse_batch(h, vbase, (const u64 *)h->stage_offs[sl].p, nullptr, nullptr, nullptr, r1 - r0, (int)max_len, false, false);
+    } else {
+      std::vector<u64> ss;
+      std::vector<u32> sl2;
+      std::vector<uint16_t> sd;
+      for (u64 r = r0; r < r1; r++) tile_sequence(offsets[r], offsets[r + 1] - offsets[r], k, SEG_MAX, 1, ss, sl2, sd);
+      rc = parse_segments(h, vbase, ss, sl2, sd, SEG_MAX, false, false);
+    }
+    if (rc) return rc;
+    CK(cudaEventRecord(h->ev_free[sl], h->s_main));
+  }
+  cudaEventDestroy(t0);
+  cudaEventDestroy(t1);
+  h->st.ms_h2d += ms_copy;
+  h->st.num_seqs += n_reads;
+  h->st.num_bases += offsets[n_reads] - offsets[0];
+  return KC_OK;
+}
+
+extern "C" int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs) {
+  if (!h) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "add after finish");
+  if (n_ctgs == 0) return KC_OK;
+  if (!seqs || !offsets || !depths) return fail(h, KC_ERR_INVALID, "null input");
+  CK(cudaSetDevice(h->cfg.device));
+  const int k = h->cfg.kmer_len;
+  std::vector<u64> ss;
+  std::vector<u32> sl;
+  std::vector<uint16_t> sd;
+  u64 inst = 0;
+  const int tile = std::min(SEG_MAX, std::max(512, 4 * (k + 2)));
+  for (u64 c = 0; c < n_ctgs; c++) {
+    const u64 len = offsets[c + 1] - offsets[c];
+    if (len < (u64)k + 2) continue;  // kcount.cpp:126
+    const double d = depths[c];
+    uint16_t depth = (uint16_t)(d > 65535 ? 65535 : d);  // contigs.hpp:57-66 get_uint16_t_depth
+    if (!depth) depth = 1;                               // kcount_cpu.cpp:75
+    inst += len - k - 1;
+    tile_sequence(offsets[c], len, k, tile, depth, ss, sl, sd);
+  }
+  decide_partitions(h, inst);
+  if (ss.empty()) return KC_OK;
+  const u64 b0 = offsets[0], b1 = offsets[n_ctgs];
+  DevBuf d_seq;
+  int rc = ensure(h, d_seq, b1 - b0 + 64);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(d_seq.p, seqs + b0, b1 - b0, cudaMemcpyHostToDevice, h->s_main));
+  rc = parse_segments(h, (const uint8_t *)d_seq.p - b0, ss, sl, sd, tile, true, true);
+  release(d_seq);
+  if (rc) return rc;
+  u32 err = 0;
+  CK(cudaMemcpy(&err, (char *)h->d_misc.p + 8, 4, cudaMemcpyDeviceToHost));
+  if (err) return fail(h, KC_ERR_BADCHAR, "contig character outside ACGTN");
+  h->has_ctg = true;
+  h->st.num_seqs += n_ctgs;
+  h->st.num_bases += b1 - b0;
+  return KC_OK;
+}
+
+namespace {
+
+struct PartWork {
+  u64 inst = 0, sup = 0;
+  u32 cap = 0;
+};
+
+template <int KW, bool CTG>
+int launch_group(kc_handle *h, const PartDesc *d_parts, const SegDesc *d_segs, int G, u32 max_chunks, u32 max_cap, const FilterArgs &fa_in,
+                 u32 *d_overflow, u32 *d_max_probe) {
+  InsertArgs ia;
+  ia.parts = d_parts;
+  ia.segs = d_segs;
+  ia.k = h->cfg.kmer_len;
+  ia.overflow = d_overflow;
+  ia.max_probe = d_max_probe;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->cfg.device);
+  const u32 resident = (u32)sms * (2048 / INS_THREADS);
+  u32 gx = std::max<u32>(1, std::min<u32>(max_chunks, (2 * resident + G - 1) / G));
+  insert_kernel<KW, CTG><<<dim3(gx, G), INS_THREADS, 0, h->s_main>>>(ia);
+  CK(cudaGetLastError());
+  FilterArgs fa = fa_in;
+  fa.parts = d_parts;
+  u32 fx = std::max<u32>(1, std::min<u32>(max_cap / 256, (2 * resident + G - 1) / G));
+  filter_kernel<KW, CTG><<<dim3(fx, G), 256, 0, h->s_main>>>(fa);
+  CK(cudaGetLastError());
+  h->st.gpu_launches += 2;
+  return KC_OK;
+}
+
+int dispatch_group(kc_handle *h, bool ctg, const PartDesc *d_parts, const SegDesc *d_segs, int G, u32 max_chunks, u32 max_cap,
+                   const FilterArgs &fa, u32 *d_overflow, u32 *d_max_probe) {
+#define GO(KWv)                                                                                                        \
+  return ctg ? launch_group<KWv, true>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe)        \
+             : launch_group<KWv, false>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe)
+  switch (h->KW) {
+    case 1: GO(1);
+    case 2: GO(2);
+    case 3: GO(3);
+    case 4: GO(4);
+  }
+#undef GO
+  return fail(h, KC_ERR_INVALID, "unsupported key width %d", h->KW);
+}
+
+}  // namespace
+
+int kc_exchange(kc_handle *h);  // kc_comm.inl
+
+extern "C" int kc_finish(kc_handle *h) {
+  if (!h) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "finish called twice");
+  CK(cudaSetDevice(h->cfg.device));
+  if (!h->P) decide_partitions(h, 0);
+  if (h->cfg.num_shards > 1) {
+    int rc = kc_exchange(h);
+    if (rc) return rc;
+  }
+  const u32 P = h->P;
+  const int KW = h->KW;
+  const u32 me = (u32)h->cfg.shard_id;
+  // every run of supermers that belongs to this shard, per partition
+  struct Src {
+    const SupHdr *hdr;
+    const u32 *payload;
+    u32 nsup, ninst;
+    bool ctg;
+  };
+  std::vector<std::vector<Src>> srcs(P);
+  bool any_ctg = false;
+  auto add_block = [&](const Block &b, u32 first_bucket) {
+    if (!b.tot_sup) return;
+    for (u32 p = 0; p < P; p++) {
+      const u32 bi = first_bucket + p;
+      if (!b.hist[bi].nsup) continue;
+      srcs[p].push_back({b.hdr + b.hdr_base[bi], b.payload + b.pay_base[bi], b.hist[bi].nsup, b.hist[bi].ninst, b.is_ctg});
+      any_ctg |= b.is_ctg;
+    }
+  };
+  for (auto &b : h->blocks) add_block(b, me * P);
+  for (auto &b : h->rblocks) add_block(b, 0);
+  const int VW = any_ctg ? VW_CTG : VW_READS;
+  const size_t slot_bytes = (size_t)KW * 8 + (size_t)VW * 4;
+
+  std::vector<PartWork> work(P);
+  u64 tot_inst = 0, read_inst = 0, ctg_inst = 0, tot_sup = 0;
+  for (u32 p = 0; p < P; p++)
+    for (auto &s : srcs[p]) {
+      work[p].inst += s.ninst;
+      work[p].sup += s.nsup;
+      (s.ctg ? ctg_inst : read_inst) += s.ninst;
+      tot_sup += s.nsup;
+    }
+  tot_inst = read_inst + ctg_inst;
+  h->st.instances_inserted = tot_inst;
+  h->st.ctg_instances_inserted = ctg_inst;
+  h->st.supermers_in = tot_sup;
+
+  // outputs: a k-mer needs count >= 2 to survive, so survivors <= read instances / 2 + contig instances
+  const u64 out_cap = read_inst / 2 + ctg_inst + 1024;
+  RC(ensure(h, h->out_keys, out_cap * KW * 8));
+  RC(ensure(h, h->out_counts, out_cap * 2));
+  RC(ensure(h, h->out_left, out_cap));
+  RC(ensure(h, h->out_right, out_cap));
+  u64 pf_cap = 0;
+  if (h->cfg.keep_prefilter) {
+    pf_cap = read_inst + 1024;
+    RC(ensure(h, h->pf_keys, pf_cap * KW * 8));
+    RC(ensure(h, h->pf_vals, pf_cap * 18));
+  }
+  DevBuf d_counters, d_overflow, d_partd, d_tab;
+  RC(ensure(h, d_counters, 64));
+  RC(ensure(h, d_overflow, (size_t)P * 4 + 4));
+  RC(ensure(h, d_partd, (size_t)P * 8));
+  CK(cudaMemsetAsync(d_counters.p, 0, 64, h->s_main));
+  CK(cudaMemsetAsync(d_overflow.p, 0, (size_t)P * 4 + 4, h->s_main));
+  CK(cudaMemsetAsync(d_partd.p, 0, (size_t)P * 8, h->s_main));
+  u32 *d_max_probe = (u32 *)d_overflow.p + P;
+
+  FilterArgs fa;
+  memset(&fa, 0, sizeof(fa));
+  fa.k = h->cfg.kmer_len;
+  fa.dmin_thres = h->cfg.dmin_thres;
+  fa.frac = 1.0 - h->cfg.dyn_min_depth;  // kcount_cpu.cpp:178, evaluated in fp64 exactly as the reference does
+  fa.overflow = (const u32 *)d_overflow.p;
+  fa.out_keys = (u64 *)h->out_keys.p;
+  fa.out_counts = (uint16_t *)h->out_counts.p;
+  fa.out_left = (char *)h->out_left.p;
+  fa.out_right = (char *)h->out_right.p;
+  fa.out_cap = out_cap;
+  fa.counters = (u64 *)d_counters.p;
+  fa.pf_keys = h->cfg.keep_prefilter ? (u64 *)h->pf_keys.p : nullptr;
+  fa.pf_vals = (uint16_t *)h->pf_vals.p;
+  fa.pf_cap = pf_cap;
+  fa.part_distinct = (u64 *)d_partd.p;
+
+  const size_t l2_budget = (size_t)(h->cfg.l2_table_mb > 0 ? h->cfg.l2_table_mb : 64) << 20;
+  const int GMAX = 64;
+  std::vector<u32> todo;
+  for (u32 p = 0; p < P; p++)
+    if (work[p].sup) todo.push_back(p);
+  double ratio = 1.0;  // distinct / instances, learned from the first group (first group is sized for the worst case)
+  std::vector<PartDesc> hparts;
+  std::vector<SegDesc> hsegs;
+  std::vector<u64> h_partd(P);
+  std::vector<u32> h_over(P + 1);
+  cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
+  CK(cudaEventRecord(e0, h->s_main));
+  int round = 0;
+  std::vector<DevBuf> desc_bufs;  // descriptor arrays of every round stay alive until the end (no reuse, no host syncs)
+  auto cap_for = [&](u32 p) {
+    u64 want = (u64)((double)work[p].inst * ratio / 0.5) + 1;
+    return std::max<u32>(256, next_pow2(want));
+  };
+  while (!todo.empty()) {
+    if (round > 0)
+      for (u32 p : todo) {
+        if ((u64)work[p].cap >= 8ull * next_pow2(work[p].inst + 1)) return fail(h, KC_ERR_CUDA, "partition table cannot grow further");
+        work[p].cap *= 4;  // retry after running out of probe slots
+      }
+    size_t nsegs_round = 0;
+    for (u32 p : todo) nsegs_round += srcs[p].size();
+    DevBuf rb_parts, rb_segs;
+    RC(ensure(h, rb_parts, todo.size() * sizeof(PartDesc)));
+    RC(ensure(h, rb_segs, nsegs_round * sizeof(SegDesc)));
+    desc_bufs.push_back(rb_parts);
+    desc_bufs.push_back(rb_segs);
+    size_t part_pos = 0, seg_pos = 0;
+    size_t pos = 0;
+    bool learned = (round > 0);
+    while (pos < todo.size()) {
+      // greedy group of partitions whose tables fit the L2 budget together
+      int G = 0;
+      size_t bytes = 0;
+      const int gmax = learned ? GMAX : 2;  // the first group only has to teach us distinct/instances
+      while (pos + G < todo.size() && G < gmax) {
+        const u32 p = todo[pos + G];
+        if (round == 0) work[p].cap = cap_for(p);
+        const size_t tb = (size_t)work[p].cap * slot_bytes;
+        if (G > 0 && bytes + tb > l2_budget) break;
+        bytes += tb;
+        G++;
+      }
+      RC(ensure(h, d_tab, bytes + 256));
+      size_t keys_total = 0;
+      for (int g = 0; g < G; g++) keys_total += (size_t)work[todo[pos + g]].cap * KW * 8;
+      size_t koff = 0, voff = 0;
+      u32 max_chunks = 0, max_cap = 0;
+      hparts.clear();
+      hsegs.clear();
+      for (int g = 0; g < G; g++) {
+        const u32 p = todo[pos + g];
+        PartDesc pd;
+        memset(&pd, 0, sizeof(pd));
+        pd.keys = (u64 *)((char *)d_tab.p + koff);
+        pd.vals = (u32 *)((char *)d_tab.p + keys_total + voff);
+        koff += (size_t)work[p].cap * KW * 8;
+        voff += (size_t)work[p].cap * VW * 4;
+        pd.cap_mask = work[p].cap - 1;
+        pd.part = p;
+        pd.seg_begin = (u32)(seg_pos + hsegs.size());
+        u32 chunk = 0;
+        for (auto &sr : srcs[p]) {
+          SegDesc sd;
+          sd.hdr = sr.hdr;
+          sd.payload = sr.payload;
+          sd.nsup = sr.nsup;
+          sd.is_ctg = sr.ctg ? 1 : 0;
+          sd.chunk0 = chunk;
+          sd.pad = 0;
+          chunk += (sr.nsup + CH - 1) / CH;
+          hsegs.push_back(sd);
+        }
+        pd.seg_end = (u32)(seg_pos + hsegs.size());
+        pd.nchunks = chunk;
+        max_chunks = std::max(max_chunks, chunk);
+        max_cap = std::max(max_cap, work[p].cap);
+        hparts.push_back(pd);
+      }
+      PartDesc *dp = (PartDesc *)rb_parts.p + part_pos;
+      SegDesc *ds = (SegDesc *)rb_segs.p;  // segments are indexed absolutely inside this round's array
+      CK(cudaMemcpyAsync(dp, hparts.data(), hparts.size() * sizeof(PartDesc), cudaMemcpyHostToDevice, h->s_main));
+      CK(cudaMemcpyAsync(ds + seg_pos, hsegs.data(), hsegs.size() * sizeof(SegDesc), cudaMemcpyHostToDevice, h->s_main));
+      part_pos += hparts.size();
+      seg_pos += hsegs.size();
+      CK(cudaMemsetAsync(d_tab.p, 0xFF, keys_total, h->s_main));
+      CK(cudaMemsetAsync((char *)d_tab.p + keys_total, 0, bytes - keys_total, h->s_main));
+      int rc = dispatch_group(h, any_ctg, dp, ds, G, max_chunks, max_cap, fa, (u32 *)d_overflow.p, d_max_probe);
+      if (rc) return rc;
+      if (!learned) {  // learn distinct/instances from the first group, then size the rest for <= ~50% load with margin
+        CK(cudaMemcpyAsync(h_partd.data(), d_partd.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->s_main));
+        CK(cudaStreamSynchronize(h->s_main));
+        double r = 0;
+        for (int g = 0; g < G; g++) {
+          const u32 p = todo[pos + g];
+          if (work[p].inst) r = std::max(r, (double)h_partd[p] / (double)work[p].inst);
+        }
+        ratio = std::min(1.0, r * 1.3 + 0.01);
+        learned = true;
+      }
+      pos += G;
+    }
+    // which partitions ran out of probe slots?
+    CK(cudaMemcpyAsync(h_over.data(), d_overflow.p, (size_t)P * 4 + 4, cudaMemcpyDeviceToHost, h->s_main));
+    CK(cudaStreamSynchronize(h->s_main));
+    std::vector<u32> again;
+    for (u32 p : todo)
+      if (h_over[p]) again.push_back(p);
+    h->st.max_probe = std::max<u64>(h->st.max_probe, h_over[P]);
+    if (!again.empty()) {
+      h->st.table_retries += again.size();
+      CK(cudaMemsetAsync(d_overflow.p, 0, (size_t)P * 4, h->s_main));
+    }
+    todo.swap(again);
+    round++;
+  }
+  for (auto &b : desc_bufs) release(b);
+  CK(cudaEventRecord(e1, h->s_main));
+  u64 counters[8];
+  CK(cudaMemcpyAsync(counters, d_counters.p, 64, cudaMemcpyDeviceToHost, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
+  h->st.ms_insert += elapsed(e0, e1);
+  release(d_counters);
+  release(d_overflow);
+  release(d_partd);
+  release(d_tab);
+  if (counters[3]) return fail(h, KC_ERR_OVERFLOW, "survivor output capacity exceeded");
+  h->n_surv = counters[0];
+  h->n_pf = counters[1];
+  h->st.distinct = counters[2];
+  h->st.survivors = counters[0];
+  h->st.purged = counters[2] - counters[0];
+  u64 inst_parsed = 0;
+  CK(cudaMemcpy(&inst_parsed, h->d_misc.p, 8, cudaMemcpyDeviceToHost));
+  h->st.instances_parsed = inst_parsed;
+  // supermer buffers are no longer needed (KmerDHT::clear_stores, kmer_dht.cpp:156-159)
+  for (auto &b : h->blocks) { cudaFree(b.hdr); cudaFree(b.payload); }
+  for (auto &b : h->rblocks) { cudaFree(b.hdr); cudaFree(b.payload); }
+  h->blocks.clear();
+  h->rblocks.clear();
+  h->finished = true;
+  return KC_OK;
+}
+
+extern "C" int kc_num_survivors(kc_handle *h, uint64_t *n) {
+  if (!h || !n) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  *n = h->n_surv;
+  return KC_OK;
+}
+
+extern "C" int kc_copy_survivors(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char *left, char *right) {
+  if (!h) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  CK(cudaSetDevice(h->cfg.device));
+  const u64 n = h->n_surv;
+  if (!n) return KC_OK;
+  if (kmer_words) CK(cudaMemcpyAsync(kmer_words, h->out_keys.p, n * h->KW * 8, cudaMemcpyDeviceToHost, h->s_main));
+  if (counts) CK(cudaMemcpyAsync(counts, h->out_counts.p, n * 2, cudaMemcpyDeviceToHost, h->s_main));
+  if (left) CK(cudaMemcpyAsync(left, h->out_left.p, n, cudaMemcpyDeviceToHost, h->s_main));
+  if (right) CK(cudaMemcpyAsync(right, h->out_right.p, n, cudaMemcpyDeviceToHost, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
+  return KC_OK;
+}
+
+extern "C" int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,
+                                   const char **d_right) {
+  if (!h) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  if (d_kmer_words) *d_kmer_words = (const uint64_t *)h->out_keys.p;
+  if (d_counts) *d_counts = (const uint16_t *)h->out_counts.p;
+  if (d_left) *d_left = (const char *)h->out_left.p;
+  if (d_right) *d_right = (const char *)h->out_right.p;
+  return KC_OK;
+}
+
+extern "C" int kc_num_prefilter(kc_handle *h, uint64_t *n) {
+  if (!h || !n) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  if (!h->cfg.keep_prefilter) return fail(h, KC_ERR_STATE, "keep_prefilter was not set");
+  *n = h->n_pf;
+  return KC_OK;
+}
+
+extern "C" int kc_copy_prefilter(kc_handle *h, uint64_t *kmer_words, uint16_t *vals9) {
+  if (!h) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  if (!h->cfg.keep_prefilter) return fail(h, KC_ERR_STATE, "keep_prefilter was not set");
+  CK(cudaSetDevice(h->cfg.device));
+  const u64 n = h->n_pf;
+  if (!n) return KC_OK;
+  CK(cudaMemcpy(kmer_words, h->pf_keys.p, n * h->KW * 8, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(vals9, h->pf_vals.p, n * 18, cudaMemcpyDeviceToHost));
+  return KC_OK;
+}
+
+extern "C" int kc_get_stats(kc_handle *h, kc_stats *st) {
+  if (!h || !st) return KC_ERR_INVALID;
+  h->st.ms_total = h->st.ms_h2d + h->st.ms_parse + h->st.ms_exchange + h->st.ms_insert + h->st.ms_filter;
+  *st = h->st;
+  return KC_OK;
+}
+
+extern "C" int kc_destroy(kc_handle *h) {
+  if (!h) return KC_OK;
+  cudaSetDevice(h->cfg.device);
+  if (h->s_main) cudaStreamSynchronize(h->s_main);
+  if (h->s_copy) cudaStreamSynchronize(h->s_copy);
+  for (auto &b : h->blocks) { cudaFree(b.hdr); cudaFree(b.payload); }
+  for (auto &b : h->rblocks) { cudaFree(b.hdr); cudaFree(b.payload); }
+  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_hist, &h->d_cursor,
+                    &h->d_hdr_base, &h->d_pay_base, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
+                    &h->pf_keys, &h->pf_vals};
+  for (DevBuf *b : bufs) release(*b);
+  if (h->ev_a) cudaEventDestroy(h->ev_a);
+  if (h->ev_b) cudaEventDestroy(h->ev_b);
+  for (int i = 0; i < 2; i++) {
+    if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]);
+    if (h->ev_free[i]) cudaEventDestroy(h->ev_free[i]);
+  }
+  if (h->s_main) cudaStreamDestroy(h->s_main);
+  if (h->s_copy) cudaStreamDestroy(h->s_copy);
+  void kc_comm_destroy(kc_handle *);
+  kc_comm_destroy(h);
+  delete h;
+  return KC_OK;
+}
+
+// ---------------------------------------------------------------- primitives for known-answer tests ----------------
+
+namespace {
+
+template <int KW>
+__global__ void prim_kmers_kernel(const char *kmers, u64 n, int k, int m, u32 num_shards, u64 *words, u64 *rcw, u64 *minim, u64 *hash,
+                                  int32_t *owner) {
+  const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const char *s = kmers + i * k;
+  // pack into the u32 stream layout the kernels use (16 bases per word, MSB first), then fetch like they do
+  u32 sb[KW * 2 + 3];
+  for (int j = 0; j < KW * 2 + 3; j++) sb[j] = 0;
+  for (int j = 0; j < k; j++) {
+    const u32 b = (u32)s[j];
+    const u32 x = (b & 4) >> 1;
+    const u32 code = x + ((x ^ (b & 2)) >> 1);
+    sb[j >> 4] |= code << (30 - 2 * (j & 15));
+  }
+  const int nw = (k + 31) >> 5;
+  const u64 last_mask = (k & 31) ? (~0ULL << (64 - 2 * (k & 31))) : ~0ULL;
+  u64 fwd[KW], rc[KW];
+  for (int j = 0; j < KW; j++) fwd[j] = (j < nw) ? fetch64(sb, 32 * j) : 0ULL;
+  for (int j = 0; j < KW; j++)
+    if (j == nw - 1) fwd[j] &= last_mask;
+  revcomp_words<KW>(fwd, rc, k);
+  u64 best = 0;
+  for (int p = 0; p + m <= k; p++) {
+    const u64 c = canonical_mmer(fetch64(sb, p), m);
+    best = c > best ? c : best;
+  }
+  for (int j = 0; j < KW; j++) {
+    words[i * KW + j] = fwd[j];
+    rcw[i * KW + j] = rc[j];
+  }
+  minim[i] = best;
+  hash[i] = murmur64_words<KW>(fwd);
+  owner[i] = (int32_t)(quick_hash(best) % num_shards);
+}
+
+__global__ void prim_get_ext_kernel(const uint16_t *rows, u64 n, int dmin_thres, double frac, char *out) {
+  const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  u32 e[4] = {rows[i * 5], rows[i * 5 + 1], rows[i * 5 + 2], rows[i * 5 + 3]};
+  out[i] = get_ext(e, rows[i * 5 + 4], dmin_thres, frac);
+}
+
+}  // namespace
+
+#define CKP(call)                                   \
+  do {                                              \
+    cudaError_t e_ = (call);                        \
+    if (e_ != cudaSuccess) { rc = KC_ERR_CUDA; goto done; } \
+  } while (0)
+
+extern "C" int kc_prim_kmers(int32_t device, int32_t k, const char *kmers, uint64_t n, int32_t num_shards, uint64_t *words,
+                             uint64_t *rc_words, uint64_t *minimizer, uint64_t *hash, int32_t *owner) {
+  if (k < 2 || k > 127 || !n) return KC_ERR_INVALID;
+  const int KW = k / 32 + 1;
+  int m = k * 2 / 3 + 1;
+  if (m < 15) m = 15;
+  if (m > 27) m = 27;
+  if (m > k) m = k;
+  int rc = KC_OK;
+  char *d_k = nullptr;
+  u64 *d_w = nullptr, *d_r = nullptr, *d_m = nullptr, *d_h = nullptr;
+  int32_t *d_o = nullptr;
+  const unsigned grid = (unsigned)((n + 127) / 128);
+  CKP(cudaSetDevice(device));
+  CKP(cudaMalloc((void **)&d_k, n * k));
+  CKP(cudaMalloc((void **)&d_w, n * KW * 8));
+  CKP(cudaMalloc((void **)&d_r, n * KW * 8));
+  CKP(cudaMalloc((void **)&d_m, n * 8));
+  CKP(cudaMalloc((void **)&d_h, n * 8));
+  CKP(cudaMalloc((void **)&d_o, n * 4));
+  CKP(cudaMemcpy(d_k, kmers, n * k, cudaMemcpyHostToDevice));
+  switch (KW) {
+    case 1: prim_kmers_kernel<1><<<grid, 128>>>(d_k, n, k, m, (u32)num_shards, d_w, d_r, d_m, d_h, d_o); break;
+    case 2: prim_kmers_kernel<2><<<grid, 128>>>(d_k, n, k, m, (u32)num_shards, d_w, d_r, d_m, d_h, d_o); break;
+    case 3: prim_kmers_kernel<3><<<grid, 128>>>(d_k, n, k, m, (u32)num_shards, d_w, d_r, d_m, d_h, d_o); break;
+    default: prim_kmers_kernel<4><<<grid, 128>>>(d_k, n, k, m, (u32)num_shards, d_w, d_r, d_m, d_h, d_o); break;
+  }
+  CKP(cudaGetLastError());
+  CKP(cudaMemcpy(words, d_w, n * KW * 8, cudaMemcpyDeviceToHost));
+  CKP(cudaMemcpy(rc_words, d_r, n * KW * 8, cudaMemcpyDeviceToHost));
+  CKP(cudaMemcpy(minimizer, d_m, n * 8, cudaMemcpyDeviceToHost));
+  CKP(cudaMemcpy(hash, d_h, n * 8, cudaMemcpyDeviceToHost));
+  CKP(cudaMemcpy(owner, d_o, n * 4, cudaMemcpyDeviceToHost));
+done:
+  cudaFree(d_k); cudaFree(d_w); cudaFree(d_r); cudaFree(d_m); cudaFree(d_h); cudaFree(d_o);
+  return rc;
+}
+
+extern "C" int kc_prim_get_ext(int32_t device, const uint16_t *acgt_count5, uint64_t n, int32_t dmin_thres, double dyn_min_depth,
+                               char *out) {
+  if (!n) return KC_ERR_INVALID;
+  int rc = KC_OK;
+  uint16_t *d_in = nullptr;
+  char *d_out = nullptr;
+  CKP(cudaSetDevice(device));
+  CKP(cudaMalloc((void **)&d_in, n * 10));
+  CKP(cudaMalloc((void **)&d_out, n));
+  CKP(cudaMemcpy(d_in, acgt_count5, n * 10, cudaMemcpyHostToDevice));
+  prim_get_ext_kernel<<<(unsigned)((n + 127) / 128), 128>>>(d_in, n, dmin_thres, 1.0 - dyn_min_depth, d_out);
+  CKP(cudaGetLastError());
+  CKP(cudaMemcpy(out, d_out, n, cudaMemcpyDeviceToHost));
+done:
+  cudaFree(d_in); cudaFree(d_out);
+  return rc;
+}
+
+#include "kc_comm.inl"

@@ -1,0 +1,195 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the CPU oracle on the same seeded inputs.
+Bar: bit-exact (identical surviving k-mer set, counts, extension chars; identical pre-filter counters)."""
+import numpy as np
+import pytest
+
+from mhm2_proxy_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+KS = [21, 31, 33, 55, 77, 99]
+
+
+def _oracle(k, rb, ro, **kw):
+    from oracle import harness
+    kind = "ref" if harness.have_ref() and kw.pop("prefer_ref", False) else "port"
+    kw.pop("prefer_ref", None)
+    return harness.run(kind, k, rb, ro, **kw)
+
+
+def _gpu(k, rb, ro, **kw):
+    from mhm2_proxy_b200 import kcount
+    return kcount.analyze_kmers(k, rb, ro, **kw)
+
+
+def _assert_same(gpu, ref, what=""):
+    keys, counts, left, right = gpu[:4]
+    assert len(keys) == len(ref.keys), f"{what}: {len(keys)} survivors vs oracle {len(ref.keys)}"
+    assert np.array_equal(keys, ref.keys), f"{what}: surviving k-mer sets differ"
+    bad = np.nonzero(counts != ref.counts)[0]
+    assert bad.size == 0, f"{what}: {bad.size} counts differ, first at {bad[:3]}: {counts[bad[:3]]} vs {ref.counts[bad[:3]]}"
+    bad = np.nonzero((left != ref.left) | (right != ref.right))[0]
+    assert bad.size == 0, f"{what}: {bad.size} extension chars differ, first {bad[:3]}"
+
+
+@pytest.fixture(scope="module")
+def community():
+    return synth.make_community(150000, n_genomes=3, seed=5)
+
+
+def test_primitives_match_oracle(built):
+    from mhm2_proxy_b200 import kcount
+    from oracle import harness
+    rng = np.random.default_rng(3)
+    for k in [15, 21, 31, 32, 33, 55, 63, 64, 65, 77, 96, 99, 127]:
+        kmers = ["".join("ACGT"[c] for c in rng.integers(0, 4, k)) for _ in range(64)]
+        kmers += ["A" * k, "T" * k, "ACGT" * (k // 4) + "ACGT"[: k % 4], "N" * k, ("ACGTN" * 30)[:k]]
+        w, r, mn, hs, ow = kcount.prim_kmers(kmers, num_shards=7)
+        for i, s in enumerate(kmers):
+            ew, er, emn, ehs, eow, _ = harness.kmer_prims("port", s, num_shards=7)
+            assert np.array_equal(w[i], ew) and np.array_equal(r[i], er), (k, s)
+            assert int(mn[i]) == emn, (k, s, hex(int(mn[i])), hex(emn))
+            assert int(hs[i]) == ehs and int(ow[i]) == eow, (k, s)
+
+
+def test_get_ext_matches_oracle(built):
+    from mhm2_proxy_b200 import kcount
+    from oracle import harness
+    rng = np.random.default_rng(4)
+    rows = []
+    for count in list(range(0, 300)) + [999, 1000, 1001, 9999, 10000, 20000, 30000, 65534, 65535]:
+        for _ in range(6):
+            e = rng.integers(0, max(2, count // 2 + 2), 4)
+            if rng.random() < 0.3:
+                e[rng.integers(0, 4)] = e[rng.integers(0, 4)]  # ties
+            rows.append(list(np.minimum(e, 65535)) + [count])
+    rows = np.asarray(rows, dtype=np.uint16)
+    for thres in (1, 2, 3):
+        got = kcount.prim_get_ext(rows, dmin_thres=thres)
+        exp = np.array([ord(harness.get_ext("port", *[int(x) for x in row], dmin_thres=thres)) for row in rows], dtype=np.uint8)
+        assert np.array_equal(got, exp), np.nonzero(got != exp)[0][:5]
+
+
+@pytest.mark.parametrize("k", KS)
+@pytest.mark.parametrize("parts", [1, 16])
+def test_reads_parity(built, community, k, parts):
+    rb, ro = synth.make_reads(8000, community, error_rate=0.01, seed=100 + k, n_rate=2e-3)
+    gpu = _gpu(k, rb, ro, num_partitions=parts, keep_prefilter=True)
+    ref = _oracle(k, rb, ro, want_prefilter=True)
+    _assert_same(gpu, ref, f"k={k} parts={parts}")
+    st, (pk, pv) = gpu[4], gpu[5]
+    assert st["instances_inserted"] == ref.stats["instances"] == synth.count_instances(ro, k)
+    assert st["distinct"] == ref.stats["distinct_after_reads"]
+    assert np.array_equal(pk, ref.pf_keys), "pre-filter key sets differ"
+    assert np.array_equal(pv, ref.pf_vals), "pre-filter counters differ"
+    assert st["dropped"] == 0
+
+
+@pytest.mark.parametrize("k", [21, 33, 99])
+def test_ragged_reads_parity(built, community, k):
+    rb, ro = synth.make_reads(6000, community, read_len=180, error_rate=0.02, seed=7 + k, n_rate=1e-3, var_len=True)
+    gpu = _gpu(k, rb, ro, num_partitions=4, batch_reads=1500)  # several internal batches
+    _assert_same(gpu, _oracle(k, rb, ro), f"ragged k={k}")
+
+
+@pytest.mark.parametrize("k", [21, 31, 55, 99])
+@pytest.mark.parametrize("thres", [2, 3])
+def test_contig_pass_parity(built, community, k, thres):
+    rb, ro = synth.make_reads(5000, community, error_rate=0.01, seed=300 + k)
+    cs, co, cd = synth.make_contigs(community, k, 120, seed=k, max_len=3000, depth_max=6)
+    gpu = _gpu(k, rb, ro, dmin_thres=thres, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd, num_partitions=8)
+    ref = _oracle(k, rb, ro, dmin_thres=thres, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd)
+    _assert_same(gpu, ref, f"ctg k={k} thres={thres}")
+    assert gpu[4]["ctg_instances_inserted"] == ref.stats["ctg_instances"]
+
+
+def test_contig_order_independence(built, community):
+    """kcount_cpu.cpp:356-406 is a sequential state machine; survivors must not depend on contig order."""
+    k = 31
+    rb, ro = synth.make_reads(3000, community, error_rate=0.01, seed=41)
+    cs, co, cd = synth.make_contigs(community, k, 80, seed=9, max_len=2000, depth_max=5, dup_frac=0.3, conflict_frac=0.1)
+    base = _oracle(k, rb, ro, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd)
+    rng = np.random.default_rng(0)
+    for _ in range(3):
+        perm = rng.permutation(len(cd))
+        seqs = [cs[int(co[i]):int(co[i + 1])] for i in perm]
+        co2 = np.zeros(len(perm) + 1, dtype=np.uint64)
+        co2[1:] = np.cumsum([len(s) for s in seqs])
+        cs2 = np.concatenate(seqs)
+        ref = _oracle(k, rb, ro, ctg_seqs=cs2, ctg_offsets=co2, ctg_depths=cd[perm])
+        assert np.array_equal(ref.keys, base.keys) and np.array_equal(ref.counts, base.counts)
+        gpu = _gpu(k, rb, ro, ctg_seqs=cs2, ctg_offsets=co2, ctg_depths=cd[perm], num_partitions=4)
+        _assert_same(gpu, base, "shuffled contigs")
+
+
+def test_long_contig_is_tiled(built, community):
+    k = 55
+    codes = community[0]
+    lut = np.frombuffer(b"ACGT", dtype=np.uint8)
+    seq = lut[codes[1000:1000 + 40000]]
+    co = np.array([0, len(seq)], dtype=np.uint64)
+    cd = np.array([7.0])
+    rb, ro = synth.make_reads(500, community, seed=77)
+    gpu = _gpu(k, rb, ro, ctg_seqs=seq, ctg_offsets=co, ctg_depths=cd)
+    _assert_same(gpu, _oracle(k, rb, ro, ctg_seqs=seq, ctg_offsets=co, ctg_depths=cd), "40 kbp contig")
+
+
+def test_long_reads_are_tiled(built, community):
+    k = 31
+    rb, ro = synth.make_reads(60, community, read_len=2500, error_rate=0.01, seed=5, paired=False)
+    _assert_same(_gpu(k, rb, ro), _oracle(k, rb, ro), "2.5 kbp reads")
+
+
+def test_saturation_and_heavy_hitters(built):
+    """One k-mer seen > 65535 times: count and extension counters saturate at 65535 (kcount_cpu.cpp:152-155,348-350)."""
+    k = 21
+    unit = np.array([0, 1, 2, 3, 1], dtype=np.uint8)  # period 5: five distinct k-mers, ~25 instances each per read
+    n = 3600
+    reads = np.tile(np.tile(unit, 30)[:150], (n, 1))
+    rb = (reads | (31 << 3)).astype(np.uint8).reshape(-1)
+    ro = np.arange(n + 1, dtype=np.uint64) * 150
+    gpu = _gpu(k, rb, ro, keep_prefilter=True, num_partitions=2)
+    ref = _oracle(k, rb, ro, want_prefilter=True)
+    assert ref.pf_vals.max() == 65535
+    _assert_same(gpu, ref, "saturation")
+    assert np.array_equal(gpu[5][1], ref.pf_vals)
+
+
+def test_edge_cases(built, community):
+    from mhm2_proxy_b200 import kcount
+    k = 31
+    # no reads at all
+    with kcount.KmerCounter(k) as kc:
+        kc.finish()
+        assert kc.num_survivors() == 0
+    # reads shorter than k+2 contribute nothing (kcount.cpp:79, kcount_cpu.cpp:84-102)
+    rb, ro = synth.make_reads(50, community, read_len=k + 1, seed=3)
+    out = _gpu(k, rb, ro)
+    assert len(out[0]) == 0 and out[4]["instances_inserted"] == 0
+    # exactly k+2 bases: one instance per read; duplicates make it survive
+    rb, ro = synth.make_reads(1, community, read_len=k + 2, seed=4, error_rate=0, lowq_tail_p=0)
+    rb3, ro3 = np.tile(rb, 3), np.arange(4, dtype=np.uint64) * (k + 2)
+    _assert_same(_gpu(k, rb3, ro3), _oracle(k, rb3, ro3), "k+2 reads")
+    # the unpaired-read dummy mate "N" (merge_reads.cpp:313-314) is skipped
+    rbn = np.concatenate([rb3, np.array([4 | (31 << 3)], dtype=np.uint8)])
+    ron = np.concatenate([ro3, np.array([ro3[-1] + 1], dtype=np.uint64)])
+    _assert_same(_gpu(k, rbn, ron), _oracle(k, rb3, ro3), "dummy N mate")
+    # errors are reported, not thrown across the ABI as crashes
+    with pytest.raises(kcount.KcountError):
+        kcount.KmerCounter(0)
+    with kcount.KmerCounter(k) as kc:
+        bad = np.frombuffer(b"ACGTXACGT" * 10, dtype=np.uint8)
+        with pytest.raises(kcount.KcountError):
+            kc.add_contigs(bad, np.array([0, len(bad)], dtype=np.uint64), np.array([3.0]))
+
+
+@pytest.mark.skipif(not __import__("oracle.harness", fromlist=["x"]).have_ref(), reason="reference build not present")
+@pytest.mark.parametrize("k", [21, 33, 99])
+def test_against_reference_build(built, community, k):
+    """Same comparison against the reference's own kcount_cpu.cpp compiled from /root/reference (oracle/_ref)."""
+    rb, ro = synth.make_reads(6000, community, error_rate=0.01, seed=900 + k, n_rate=1e-3)
+    cs, co, cd = synth.make_contigs(community, k, 40, seed=k + 1)
+    gpu = _gpu(k, rb, ro, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd, num_partitions=8)
+    ref = _oracle(k, rb, ro, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd, prefer_ref=True)
+    assert ref.stats["dropped"] == 0 and ref.stats["singleton_overrides"] == 0
+    _assert_same(gpu, ref, f"reference build k={k}")
