@@ -65,9 +65,14 @@ typedef struct kc_stats {
   uint64_t table_retries;       /* partitions re-run with a larger table */
   uint64_t max_probe;
   uint64_t num_partitions;
-  double ms_h2d, ms_parse, ms_exchange, ms_insert, ms_filter, ms_total; /* CUDA-event times, this handle */
+  /* CUDA-event times on the library's own stream, summed over launches. ms_parse = parse_count + parse_fill kernels
+   * plus the bucket-layout round trip between them; ms_insert / ms_filter / ms_clear = those kernels only. */
+  double ms_h2d, ms_parse, ms_exchange, ms_insert, ms_filter, ms_total;
+  double ms_parse_count, ms_parse_fill, ms_clear, ms_finish;
   uint64_t gpu_launches;        /* kernels launched by this handle so far */
-  uint64_t reserved[8];
+  uint64_t n_parse_launches, n_insert_launches, n_filter_launches;
+  uint64_t table_bytes_max;     /* largest group of partition tables built at once (the L2-resident working set) */
+  uint64_t reserved[4];
 } kc_stats;
 
 void kc_config_default(kc_config *cfg, int32_t kmer_len);

@@ -49,7 +49,7 @@ struct kc_handle {
   u32 P = 0;  // partitions per shard (0 until the first add decides)
   bool finished = false, has_ctg = false;
   cudaStream_t s_main = nullptr, s_copy = nullptr;
-  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
   std::vector<Block> blocks;       // produced locally
   std::vector<Block> rblocks;      // received from peers (multi-shard)
   DevBuf stage_bytes[2], stage_offs[2];
@@ -161,6 +161,8 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
   CK(cudaEventCreate(&h->ev_a));
   CK(cudaEventCreate(&h->ev_b));
+  CK(cudaEventCreate(&h->ev_c));
+  CK(cudaEventCreate(&h->ev_d));
   for (int i = 0; i < 2; i++) {
     CK(cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
@@ -240,7 +242,9 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   a.hist = (BucketHist *)h->d_hist.p;
   parse_kernel<false><<<grid, warps * 32, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
+  h->st.n_parse_launches++;
   CK(cudaGetLastError());
+  CK(cudaEventRecord(h->ev_c, h->s_main));
   Block blk;
   blk.is_ctg = is_ctg;
   blk.hist.resize(NP);
@@ -275,12 +279,16 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   a.pay_base = (const u64 *)h->d_pay_base.p;
   a.hdr = blk.hdr;
   a.payload = blk.payload;
+  CK(cudaEventRecord(h->ev_d, h->s_main));
   parse_kernel<true><<<grid, warps * 32, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
+  h->st.n_parse_launches++;
   CK(cudaGetLastError());
   CK(cudaEventRecord(e1, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));  // hdr_base/pay_base host vectors are about to move; also surfaces kernel faults here
   h->st.ms_parse += elapsed(e0, e1);
+  h->st.ms_parse_count += elapsed(e0, h->ev_c);
+  h->st.ms_parse_fill += elapsed(h->ev_d, e1);
   h->st.supermers_out += hs;
   h->st.supermer_bytes_out += hs * sizeof(SupHdr) + ps * 4;
   h->blocks.push_back(std::move(blk));
@@ -473,7 +481,7 @@ struct PartWork {
 
 template <int KW, bool CTG>
 int launch_group(kc_handle *h, const PartDesc *d_parts, const SegDesc *d_segs, int G, u32 max_chunks, u32 max_cap, const FilterArgs &fa_in,
-                 u32 *d_overflow, u32 *d_max_probe) {
+                 u32 *d_overflow, u32 *d_max_probe, cudaEvent_t *ev3) {
   InsertArgs ia;
   ia.parts = d_parts;
   ia.segs = d_segs;
@@ -484,22 +492,27 @@ int launch_group(kc_handle *h, const PartDesc *d_parts, const SegDesc *d_segs, i
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->cfg.device);
   const u32 resident = (u32)sms * (2048 / INS_THREADS);
   u32 gx = std::max<u32>(1, std::min<u32>(max_chunks, (2 * resident + G - 1) / G));
+  CK(cudaEventRecord(ev3[0], h->s_main));
   insert_kernel<KW, CTG><<<dim3(gx, G), INS_THREADS, 0, h->s_main>>>(ia);
   CK(cudaGetLastError());
+  CK(cudaEventRecord(ev3[1], h->s_main));
   FilterArgs fa = fa_in;
   fa.parts = d_parts;
   u32 fx = std::max<u32>(1, std::min<u32>(max_cap / 256, (2 * resident + G - 1) / G));
   filter_kernel<KW, CTG><<<dim3(fx, G), 256, 0, h->s_main>>>(fa);
   CK(cudaGetLastError());
+  CK(cudaEventRecord(ev3[2], h->s_main));
   h->st.gpu_launches += 2;
+  h->st.n_insert_launches++;
+  h->st.n_filter_launches++;
   return KC_OK;
 }
 
 int dispatch_group(kc_handle *h, bool ctg, const PartDesc *d_parts, const SegDesc *d_segs, int G, u32 max_chunks, u32 max_cap,
-                   const FilterArgs &fa, u32 *d_overflow, u32 *d_max_probe) {
+                   const FilterArgs &fa, u32 *d_overflow, u32 *d_max_probe, cudaEvent_t *ev3) {
 #define GO(KWv)                                                                                                        \
-  return ctg ? launch_group<KWv, true>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe)        \
-             : launch_group<KWv, false>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe)
+  return ctg ? launch_group<KWv, true>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe, ev3)   \
+             : launch_group<KWv, false>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe, ev3)
   switch (h->KW) {
     case 1: GO(1);
     case 2: GO(2);
@@ -614,6 +627,7 @@ extern "C" int kc_finish(kc_handle *h) {
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
   int round = 0;
+  std::vector<cudaEvent_t> group_events;  // 4 per group: before clear, before insert, after insert, after filter
   std::vector<DevBuf> desc_bufs;  // descriptor arrays of every round stay alive until the end (no reuse, no host syncs)
   auto cap_for = [&](u32 p) {
     u64 want = (u64)((double)work[p].inst * ratio / 0.5) + 1;
@@ -690,9 +704,16 @@ extern "C" int kc_finish(kc_handle *h) {
       CK(cudaMemcpyAsync(ds + seg_pos, hsegs.data(), hsegs.size() * sizeof(SegDesc), cudaMemcpyHostToDevice, h->s_main));
       part_pos += hparts.size();
       seg_pos += hsegs.size();
+      cudaEvent_t ev4[4];
+      for (auto &e : ev4) {
+        CK(cudaEventCreate(&e));
+        group_events.push_back(e);
+      }
+      h->st.table_bytes_max = std::max<u64>(h->st.table_bytes_max, bytes);
+      CK(cudaEventRecord(ev4[0], h->s_main));
       CK(cudaMemsetAsync(d_tab.p, 0xFF, keys_total, h->s_main));
       CK(cudaMemsetAsync((char *)d_tab.p + keys_total, 0, bytes - keys_total, h->s_main));
-      int rc = dispatch_group(h, any_ctg, dp, ds, G, max_chunks, max_cap, fa, (u32 *)d_overflow.p, d_max_probe);
+      int rc = dispatch_group(h, any_ctg, dp, ds, G, max_chunks, max_cap, fa, (u32 *)d_overflow.p, d_max_probe, ev4 + 1);
       if (rc) return rc;
       if (!learned) {  // learn distinct/instances from the first group, then size the rest for <= ~50% load with margin
         CK(cudaMemcpyAsync(h_partd.data(), d_partd.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->s_main));
@@ -726,7 +747,13 @@ extern "C" int kc_finish(kc_handle *h) {
   u64 counters[8];
   CK(cudaMemcpyAsync(counters, d_counters.p, 64, cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
-  h->st.ms_insert += elapsed(e0, e1);
+  h->st.ms_finish += elapsed(e0, e1);
+  for (size_t g = 0; g + 3 < group_events.size(); g += 4) {
+    h->st.ms_clear += elapsed(group_events[g], group_events[g + 1]);
+    h->st.ms_insert += elapsed(group_events[g + 1], group_events[g + 2]);
+    h->st.ms_filter += elapsed(group_events[g + 2], group_events[g + 3]);
+  }
+  for (auto e : group_events) cudaEventDestroy(e);
   release(d_counters);
   release(d_overflow);
   release(d_partd);
@@ -803,7 +830,7 @@ extern "C" int kc_copy_prefilter(kc_handle *h, uint64_t *kmer_words, uint16_t *v
 
 extern "C" int kc_get_stats(kc_handle *h, kc_stats *st) {
   if (!h || !st) return KC_ERR_INVALID;
-  h->st.ms_total = h->st.ms_h2d + h->st.ms_parse + h->st.ms_exchange + h->st.ms_insert + h->st.ms_filter;
+  h->st.ms_total = h->st.ms_parse + h->st.ms_exchange + h->st.ms_finish;
   *st = h->st;
   return KC_OK;
 }
@@ -821,6 +848,8 @@ extern "C" int kc_destroy(kc_handle *h) {
   for (DevBuf *b : bufs) release(*b);
   if (h->ev_a) cudaEventDestroy(h->ev_a);
   if (h->ev_b) cudaEventDestroy(h->ev_b);
+  if (h->ev_c) cudaEventDestroy(h->ev_c);
+  if (h->ev_d) cudaEventDestroy(h->ev_d);
   for (int i = 0; i < 2; i++) {
     if (h->ev_copy[i]) cudaEventDestroy(h->ev_copy[i]);
     if (h->ev_free[i]) cudaEventDestroy(h->ev_free[i]);

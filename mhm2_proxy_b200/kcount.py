@@ -29,8 +29,10 @@ class KcStats(C.Structure):
         "num_seqs", "num_bases", "instances_parsed", "instances_inserted", "ctg_instances_inserted", "supermers_out",
         "supermer_bytes_out", "supermer_bytes_sent", "supermers_in", "distinct", "purged", "survivors", "dropped",
         "table_retries", "max_probe", "num_partitions")] + [(n, C.c_double) for n in (
-            "ms_h2d", "ms_parse", "ms_exchange", "ms_insert", "ms_filter", "ms_total")] + [
-                ("gpu_launches", C.c_uint64), ("reserved", C.c_uint64 * 8)]
+            "ms_h2d", "ms_parse", "ms_exchange", "ms_insert", "ms_filter", "ms_total", "ms_parse_count", "ms_parse_fill",
+            "ms_clear", "ms_finish")] + [(n, C.c_uint64) for n in (
+                "gpu_launches", "n_parse_launches", "n_insert_launches", "n_filter_launches", "table_bytes_max")] + [
+                    ("reserved", C.c_uint64 * 4)]
 
 
 EXPORTS = [

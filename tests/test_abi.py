@@ -30,7 +30,7 @@ def test_struct_layouts_match_header(built):
     assert (cfg.kmer_len, cfg.qual_cutoff, cfg.dmin_thres, cfg.num_shards) == (31, 20, 2, 1)
     assert abs(cfg.dyn_min_depth - 0.9) < 1e-15
     assert ctypes.sizeof(kcount.KcConfig) == 80
-    assert ctypes.sizeof(kcount.KcStats) == 16 * 8 + 6 * 8 + 8 + 8 * 8
+    assert ctypes.sizeof(kcount.KcStats) == 16 * 8 + 10 * 8 + 5 * 8 + 4 * 8
 
 
 def test_no_gpu_means_loud_failure(built):
