@@ -175,3 +175,77 @@ def get_ext(kind, a, c, g, t, count, dmin_thres=2):
     lib, pfx = _lib(kind)
     fn = getattr(lib, pfx + ("get_ext4" if kind == "port" else "get_ext"))
     return fn(a, c, g, t, count, dmin_thres).decode()
+
+
+# ---- P-rank timed baseline: the reference's code, one process per emulated UPC++ rank (ref_driver.cpp phase_a/phase_b) ----
+
+def _phase_main(argv):
+    """Entry of one emulated rank (a separate `python oracle/harness.py phase ...` process). Prints one JSON line."""
+    import json
+    phase, k, P, me, prefix, dmin_thres, num_elems = argv[0], int(argv[1]), int(argv[2]), int(argv[3]), argv[4], int(argv[5]), int(argv[6])
+    lib = C.CDLL(REF_SO)
+    if phase == "a":
+        rb = np.ascontiguousarray(np.load(prefix + "_bytes.npy", mmap_mode="r"))
+        ro = np.ascontiguousarray(np.load(prefix + "_offs.npy", mmap_mode="r"))
+        n = len(ro) - 1
+        r0, r1 = n * me // P, n * (me + 1) // P
+        lib.oref_phase_a.restype = C.c_double
+        lib.oref_phase_a.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_char_p,
+                                     C.c_void_p]
+        inst = np.zeros(1, dtype=np.uint64)
+        t = lib.oref_phase_a(k, 33, P, me, _p(rb), _p(ro), r0, r1, prefix.encode(), _p(inst))
+        print(json.dumps([t, int(inst[0]), 0]))
+        return
+    lib.oref_phase_b.restype = C.c_double
+    lib.oref_phase_b.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    surv = np.zeros(1, dtype=np.uint64)
+    dist = np.zeros(1, dtype=np.uint64)
+    t = lib.oref_phase_b(k, dmin_thres, P, me, prefix.encode(), num_elems, _p(surv), _p(dist))
+    print(json.dumps([t, int(surv[0]), int(dist[0])]))
+
+
+def run_multirank(k, read_bytes, read_offsets, P, dmin_thres=2, workdir=None, timeout=1200):
+    """Time the reference kcount with P emulated ranks on P processes. Returns dict(seconds, instances, survivors, ...).
+    seconds = max over ranks of phase A + max over ranks of phase B (bulk-synchronous, like a barrier between them)."""
+    import glob
+    import json
+    import sys
+    import tempfile
+    if not have_ref():
+        raise FileNotFoundError(REF_SO)
+    base = workdir or ("/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir())
+    d = tempfile.mkdtemp(prefix="kcref_", dir=base)
+    prefix = os.path.join(d, "x")
+    try:
+        np.save(prefix + "_bytes.npy", np.ascontiguousarray(read_bytes, dtype=np.uint8))
+        np.save(prefix + "_offs.npy", np.ascontiguousarray(read_offsets, dtype=np.uint64))
+        lens = np.diff(np.asarray(read_offsets).astype(np.int64))
+        inst = int(np.maximum(lens - k - 1, 0).sum())
+        num_elems = max(1000, int(inst * 1.3 / P))
+
+        def phase(ph):
+            procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "phase", ph, str(k), str(P), str(me), prefix,
+                                       str(dmin_thres), str(num_elems)], stdout=subprocess.PIPE, text=True) for me in range(P)]
+            out = []
+            for pr in procs:
+                o, _ = pr.communicate(timeout=timeout)
+                if pr.returncode:
+                    raise RuntimeError(f"reference rank process failed in phase {ph}")
+                out.append(json.loads(o.strip().splitlines()[-1]))
+            return out
+
+        ra = phase("a")
+        rbb = phase("b")
+        ta, tb = max(r[0] for r in ra), max(r[0] for r in rbb)
+        return dict(seconds=ta + tb, seconds_parse=ta, seconds_insert=tb, instances=sum(r[1] for r in ra),
+                    survivors=sum(r[1] for r in rbb), distinct=sum(r[2] for r in rbb), ranks=P)
+    finally:
+        for f in glob.glob(os.path.join(d, "*")):
+            os.remove(f)
+        os.rmdir(d)
+
+
+if __name__ == "__main__":
+    import sys
+    if len(sys.argv) > 1 and sys.argv[1] == "phase":
+        _phase_main(sys.argv[2:])

@@ -277,3 +277,122 @@ char oref_get_ext(uint16_t a, uint16_t c, uint16_t g, uint16_t t, uint16_t count
   return e.get_ext(count);
 }
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// P-rank emulation for the timed CPU baseline: the reference's algorithm and code, with the GASNet
+// transport replaced by files in shared memory. Phase A: rank `me` runs the reference's process_seq over ITS reads with
+// rank_n() = P; the shim's aggregating store hands every (target, supermer) to a tap that appends it to a per-target
+// buffer, written to <prefix>_<me>_<target>.bin. Phase B: rank `me` feeds every <prefix>_*_<me>.bin to the reference's
+// HashTableInserter::insert_supermer, then flush + insert_into_local_hashtable. Each phase is run by P processes.
+namespace {
+template <int MAX_K>
+double phase_a(int k, int qual_offset, int P, int me, const uint8_t *bytes, const uint64_t *offs, uint64_t r0, uint64_t r1,
+               const char *prefix, uint64_t *out_inst) {
+  using clk = std::chrono::steady_clock;
+  Kmer<MAX_K>::set_k(k);
+  upcxx::shim_state::nranks() = P;
+  upcxx::shim_state::me() = me;
+  upcxx_utils::shim_mem::free_mem() = 1e9;
+  std::vector<std::string> bufs(P);
+  upcxx_utils::ThreeTierAggrStore<Supermer>::tap() = [&bufs](int target, const Supermer &s) {
+    std::string &b = bufs[target];
+    uint32_t len = (uint32_t)s.seq.size();
+    uint16_t cnt = s.count;
+    b.append((const char *)&cnt, 2);
+    b.append((const char *)&len, 4);
+    b.append(s.seq);
+    return true;
+  };
+  dist_object<KmerDHT<MAX_K>> kmer_dht((uint64_t)1000, (int)0, (int)100, false, false);
+  auto t0 = clk::now();
+  SeqBlockInserter<MAX_K> sbi(qual_offset, kmer_dht->get_minimizer_len());
+  static const char nucleotide_map[8] = {'A', 'C', 'G', 'T', 'N', 'N', 'N', 'N'};
+  std::string seq;
+  uint64_t inst = 0;
+  for (uint64_t r = r0; r < r1; r++) {
+    size_t len = offs[r + 1] - offs[r];
+    if (len < (size_t)k + 2) continue;
+    seq.resize(len);
+    const uint8_t *b = bytes + offs[r];
+    for (size_t i = 0; i < len; i++) {
+      char c = nucleotide_map[b[i] & 7];
+      if ((b[i] >> 3) < KCOUNT_QUAL_CUTOFF) c = tolower(c);
+      seq[i] = c;
+    }
+    sbi.process_seq(seq, 0, kmer_dht);
+    inst += len - k - 1;
+  }
+  for (int t = 0; t < P; t++) {
+    std::string fn = std::string(prefix) + "_" + std::to_string(me) + "_" + std::to_string(t) + ".bin";
+    FILE *f = fopen(fn.c_str(), "wb");
+    if (f) { fwrite(bufs[t].data(), 1, bufs[t].size(), f); fclose(f); }
+  }
+  auto t1 = clk::now();
+  upcxx_utils::ThreeTierAggrStore<Supermer>::tap() = nullptr;
+  *out_inst = inst;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
+template <int MAX_K>
+double phase_b(int k, int dmin_thres, int P, int me, const char *prefix, uint64_t num_elems, uint64_t *out_surv, uint64_t *out_distinct) {
+  using clk = std::chrono::steady_clock;
+  Kmer<MAX_K>::set_k(k);
+  upcxx::shim_state::nranks() = P;
+  upcxx::shim_state::me() = me;
+  upcxx_utils::shim_mem::free_mem() = 3.2 * (double)num_elems * (8 * (k / 32 + 1) + 20) / 0.6;
+  _dmin_thres = dmin_thres;
+  dist_object<KmerDHT<MAX_K>> kmer_dht((uint64_t)num_elems, (int)0, (int)100, false, false);
+  auto t0 = clk::now();
+  std::string buf;
+  for (int src = 0; src < P; src++) {
+    std::string fn = std::string(prefix) + "_" + std::to_string(src) + "_" + std::to_string(me) + ".bin";
+    FILE *f = fopen(fn.c_str(), "rb");
+    if (!f) continue;
+    fseek(f, 0, SEEK_END);
+    long sz = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    buf.resize(sz);
+    if (sz && fread(&buf[0], 1, sz, f) != (size_t)sz) { fclose(f); continue; }
+    fclose(f);
+    size_t pos = 0;
+    std::string seq;
+    while (pos + 6 <= (size_t)sz) {
+      uint16_t cnt; uint32_t len;
+      memcpy(&cnt, &buf[pos], 2); memcpy(&len, &buf[pos + 2], 4);
+      pos += 6;
+      seq.assign(&buf[pos], len);
+      pos += len;
+      kmer_dht->ht_inserter->insert_supermer(seq, cnt);  // what the store's update_func does (kmer_dht.cpp:146-149)
+    }
+  }
+  *out_distinct = kmer_dht->ht_inserter->state->kmers->size();
+  kmer_dht->flush_updates();
+  kmer_dht->finish_updates();
+  auto t1 = clk::now();
+  *out_surv = kmer_dht->get_local_num_kmers();
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+}  // namespace
+
+extern "C" {
+double oref_phase_a(int k, int qual_offset, int P, int me, const uint8_t *bytes, const uint64_t *offs, uint64_t r0, uint64_t r1,
+                    const char *prefix, uint64_t *out_inst) {
+  switch ((k / 32 + 1) * 32) {
+    case 32: return phase_a<32>(k, qual_offset, P, me, bytes, offs, r0, r1, prefix, out_inst);
+    case 64: return phase_a<64>(k, qual_offset, P, me, bytes, offs, r0, r1, prefix, out_inst);
+    case 96: return phase_a<96>(k, qual_offset, P, me, bytes, offs, r0, r1, prefix, out_inst);
+    case 128: return phase_a<128>(k, qual_offset, P, me, bytes, offs, r0, r1, prefix, out_inst);
+  }
+  return -1;
+}
+double oref_phase_b(int k, int dmin_thres, int P, int me, const char *prefix, uint64_t num_elems, uint64_t *out_surv,
+                    uint64_t *out_distinct) {
+  switch ((k / 32 + 1) * 32) {
+    case 32: return phase_b<32>(k, dmin_thres, P, me, prefix, num_elems, out_surv, out_distinct);
+    case 64: return phase_b<64>(k, dmin_thres, P, me, prefix, num_elems, out_surv, out_distinct);
+    case 96: return phase_b<96>(k, dmin_thres, P, me, prefix, num_elems, out_surv, out_distinct);
+    case 128: return phase_b<128>(k, dmin_thres, P, me, prefix, num_elems, out_surv, out_distinct);
+  }
+  return -1;
+}
+}
