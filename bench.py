@@ -155,7 +155,7 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup if args.ref_warm else 0, "ms_per_step": 1000 * secs / args.steps, "wall_s": wall,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": workload_config(args, n_sample, 1),
+        "config": workload_config(args, args.reads, args.gpus),
         "cpu_baseline": cb,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -168,3 +168,184 @@ def workload_config(args, reads_per_gpu, n_gpus):
             "genome_bp": GENOME_BP, "n_genomes": N_GENOMES, "error_rate": ERR, "dmin_thres": 2,
             "l2_flush": "inputs (>= 2 GB) and supermer buffers are far larger than the 126 MB L2; nothing is reused across steps",
             "parallelism": f"reads split across {n_gpus} GPU(s), table hash-sharded by quick_hash(minimizer) % {n_gpus}"}
+
+
+def one_pass(kcount, k, args, rank, world, dev, mode, tb, to, d_b, d_o, uid):
+    """One kcount round at one k. mode 'device': reads already in HBM; 'host': pinned host buffers + D2H of survivors."""
+    n = to.numel() - 1
+    inst_hint = n * (READ_LEN - k - 1)
+    kc = kcount.KmerCounter(k, num_shards=world, shard_id=rank, device=dev, expected_instances=inst_hint,
+                            num_partitions=args.partitions, l2_table_mb=args.l2_mb)
+    try:
+        if world > 1:
+            kc.comm_init(uid)
+        if mode == "device":
+            kc.add_reads_device(d_b.data_ptr(), d_o.data_ptr(), n, d_b.numel(), READ_LEN)
+        else:
+            kc.add_reads_ptr(tb.data_ptr(), to.data_ptr(), n)
+        kc.finish()
+        d2h = 0
+        if mode == "host":
+            keys, counts, left, right = kc.survivors(sort=False)
+            d2h = keys.nbytes + counts.nbytes + left.nbytes + right.nbytes
+        st = kc.stats()
+        st["d2h_bytes"] = d2h
+        return st
+    finally:
+        kc.close()
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from mhm2_proxy_b200 import kcount
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the kcount path is CUDA only (use --impl reference for the CPU arm)")
+    kcount.load_library()
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    uid = None
+    if world > 1:
+        box = [kcount.KmerCounter.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        uid = box[0]
+
+    n_reads = args.reads
+    t0 = time.time()
+    tb, to = gen_reads(n_reads, seed=0xB200_0002 + 7919 * rank)
+    t_gen = time.time() - t0
+    d_b = tb.cuda(non_blocking=True)
+    d_o = to.cuda(non_blocking=True)
+    torch.cuda.synchronize()
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(mode, steps, warmup, sampler=None):
+        for _ in range(warmup):
+            for k in args.ks:
+                one_pass(kcount, k, args, rank, world, local, mode, tb, to, d_b, d_o, uid)
+        sync()
+        if sampler:
+            sampler.start()
+        stats = []
+        t_start = time.perf_counter()
+        for _ in range(steps):
+            for k in args.ks:
+                stats.append(one_pass(kcount, k, args, rank, world, local, mode, tb, to, d_b, d_o, uid))
+        sync()
+        el = time.perf_counter() - t_start
+        clocks = sampler.stop() if sampler else None
+        if world > 1:
+            t = torch.tensor([el], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            el = float(t.item())
+        return el, stats, clocks
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    el, stats, clocks = timed("device", args.steps, args.warmup, sampler)
+    inst_local = sum(s["instances_parsed"] for s in stats)
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    el2, stats2, _ = timed("host", e2e_steps, 1)
+    inst2_local = sum(s["instances_parsed"] for s in stats2)
+    if world > 1:
+        t = torch.tensor([inst_local, inst2_local], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        inst_all, inst2_all = float(t[0].item()), float(t[1].item())
+    else:
+        inst_all, inst2_all = float(inst_local), float(inst2_local)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # per-kernel device times (CUDA events on the library's stream, summed over the timed steps of rank 0)
+    kern = {}
+    for name, key in (("parse_kernel<COUNT>", "ms_parse_count"), ("parse_kernel<FILL>", "ms_parse_fill"), ("insert_kernel", "ms_insert"),
+                      ("filter_kernel", "ms_filter"), ("table clear (memset)", "ms_clear")):
+        kern[name] = sum(s[key] for s in stats)
+    launches = {"parse_kernel<COUNT>": sum(s["n_parse_launches"] for s in stats) // 2,
+                "parse_kernel<FILL>": sum(s["n_parse_launches"] for s in stats) // 2,
+                "insert_kernel": sum(s["n_insert_launches"] for s in stats), "filter_kernel": sum(s["n_filter_launches"] for s in stats)}
+    dom = max((n for n in kern if n in launches), key=lambda n: kern[n])
+    peak, peak_src = hbm_peak()
+    per_k = {}
+    alg_bytes = 0.0
+    for k in args.ks:
+        sk = [s for s, kk in zip(stats, list(args.ks) * args.steps) if kk == k]
+        ik = sum(s["instances_parsed"] for s in sk)
+        alg_bytes += ik * b_alg(k)
+        per_k[str(k)] = {"instances_per_pass": sk[0]["instances_parsed"], "distinct": sk[0]["distinct"], "survivors": sk[0]["survivors"],
+                         "partitions": sk[0]["num_partitions"], "supermers": sk[0]["supermers_out"],
+                         "supermer_bytes": sk[0]["supermer_bytes_out"], "table_retries": sk[0]["table_retries"],
+                         "table_group_bytes_max": sk[0]["table_bytes_max"],
+                         "ms": {kk: round(sum(s[kk] for s in sk) / len(sk), 3) for kk in
+                                ("ms_parse_count", "ms_parse_fill", "ms_parse", "ms_clear", "ms_insert", "ms_filter", "ms_finish")},
+                         "b_alg": round(b_alg(k), 2)}
+    achieved = alg_bytes / (kern[dom] * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get(dom)
+        except Exception:
+            traffic = None
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        cpu = reference_rate(tb, to, min(n_reads, args.ref_reads or 40_000 * cores), args.ks, cores)
+    value = inst_all / el
+    h2d = (tb.numel() + to.numel() * 8) * len(args.ks)
+    d2h = sum(s["d2h_bytes"] for s in stats2) / e2e_steps
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1000 * el / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic", "config": workload_config(args, n_reads, world),
+        "timing": "wall clock around K steps, torch.cuda.synchronize (+barrier) on both sides, max over ranks; per-kernel times "
+                  "are CUDA events on the library's stream",
+        "e2e": {"value": inst2_all / el2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
+                "steps": e2e_steps, "ms_per_step": 1000 * el2 / e2e_steps},
+        "gpu_launches": int(sum(s["gpu_launches"] for s in stats)),
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "peak_source": peak_src, "launches": launches[dom],
+                     "avg_launch_ms": kern[dom] / max(1, launches[dom]),
+                     "algorithmic_bytes": "B_alg(k) = L/(L-k-1) + W + 12 per instance x instances of the timed steps (DESIGN.md)",
+                     "pipeline_frac": (alg_bytes / el / 1e9) / peak},
+        "kernel_ms": {k_: round(v, 3) for k_, v in kern.items()}, "per_k": per_k,
+        "cpu_baseline": cpu, "clocks": clocks, "gen_s": round(t_gen, 1),
+    }
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads", type=int, default=C2_READS, help="reads per GPU")
+    ap.add_argument("--ks", type=lambda s: tuple(int(x) for x in s.split(",")), default=C2_KS)
+    ap.add_argument("--partitions", type=int, default=0)
+    ap.add_argument("--l2-mb", dest="l2_mb", type=int, default=0)
+    ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=2)
+    ap.add_argument("--ref-reads", dest="ref_reads", type=int, default=0, help="reads in the CPU sample (default 40k per core)")
+    ap.add_argument("--ref-warm", dest="ref_warm", action="store_true", help="also run warm-up passes in --impl reference")
+    ap.add_argument("--no-cpu", dest="no_cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
