@@ -210,9 +210,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     uid = None
     if world > 1:
-        box = [kcount.KmerCounter.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        uid = box[0]
+        from mhm2_proxy_b200.dist import share_unique_id
+        uid = share_unique_id(rank, kcount.KmerCounter.comm_unique_id)
 
     n_reads = args.reads
     t0 = time.time()

@@ -99,6 +99,10 @@ int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, cons
 int kc_comm_unique_id(uint8_t id128[128]);
 int kc_comm_init(kc_handle *h, const uint8_t id128[128]);
 
+/* several shards inside ONE process (handles[i] = shard i of n, any devices): exchange by peer copies, then finish all.
+ * Same role as kc_comm_init + kc_finish on every rank; used by tests and by single-process multi-GPU drivers. */
+int kc_finish_local_group(kc_handle **handles, int32_t n);
+
 /* KmerDHT::flush_updates + finish_updates -> HashTableInserter::insert_into_local_hashtable
  * (kmer_dht.cpp:227-236, kcount_cpu.cpp:490-528). Collective across shards when num_shards > 1. */
 int kc_finish(kc_handle *h);

@@ -187,6 +187,8 @@ void decide_partitions(kc_handle *h, u64 inst_estimate) {
     h->P = std::min<u32>(p, 8192u);
   }
   while ((u64)h->P * (u64)h->cfg.num_shards > 65536ull) h->P >>= 1;  // bucket ids are u16 inside the parse kernel
+  // NOTE multi-shard: every shard must arrive at the same P (checked at exchange time); give all shards the same
+  // cfg.num_partitions or cfg.expected_instances.
   h->st.num_partitions = h->P;
 }
 
@@ -526,6 +528,7 @@ int dispatch_group(kc_handle *h, bool ctg, const PartDesc *d_parts, const SegDes
 }  // namespace
 
 int kc_exchange(kc_handle *h);  // kc_comm.inl
+int finish_count(kc_handle *h);
 
 extern "C" int kc_finish(kc_handle *h) {
   if (!h) return KC_ERR_INVALID;
@@ -536,6 +539,12 @@ extern "C" int kc_finish(kc_handle *h) {
     int rc = kc_exchange(h);
     if (rc) return rc;
   }
+  return finish_count(h);
+}
+
+// the count phase of one shard: every supermer that belongs to it is in h->blocks (own buckets) or h->rblocks (received)
+int finish_count(kc_handle *h) {
+  CK(cudaSetDevice(h->cfg.device));
   const u32 P = h->P;
   const int KW = h->KW;
   const u32 me = (u32)h->cfg.shard_id;

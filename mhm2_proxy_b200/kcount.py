@@ -37,7 +37,7 @@ class KcStats(C.Structure):
 
 EXPORTS = [
     "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_add_reads", "kc_add_reads_device", "kc_add_contigs",
-    "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
+    "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
 ]
 
@@ -66,6 +66,7 @@ def load_library():
     lib.kc_comm_unique_id.argtypes = [vp]
     lib.kc_comm_init.argtypes = [vp, vp]
     lib.kc_finish.argtypes = [vp]
+    lib.kc_finish_local_group.argtypes = [C.POINTER(vp), i32]
     lib.kc_num_survivors.argtypes = [vp, C.POINTER(u64)]
     lib.kc_copy_survivors.argtypes = [vp, vp, vp, vp, vp]
     lib.kc_survivors_device.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
@@ -208,6 +209,16 @@ class KmerCounter:
 
     def __exit__(self, *a):
         self.close()
+
+
+def finish_local_group(counters):
+    """Finish shards 0..n-1 that all live in this process (kc_finish_local_group)."""
+    lib = load_library()
+    arr = (C.c_void_p * len(counters))(*[c.h for c in counters])
+    rc = lib.kc_finish_local_group(arr, len(counters))
+    if rc != KC_OK:
+        msgs = "; ".join(lib.kc_last_error(c.h).decode() for c in counters)
+        raise KcountError(f"kc_finish_local_group failed ({ERR_NAMES.get(rc, rc)}): {msgs}")
 
 
 def analyze_kmers(kmer_len, read_bytes, read_offsets, dmin_thres=2, ctg_seqs=None, ctg_offsets=None, ctg_depths=None, **kw):

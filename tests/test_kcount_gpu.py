@@ -193,3 +193,52 @@ def test_against_reference_build(built, community, k):
     ref = _oracle(k, rb, ro, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd, prefer_ref=True)
     assert ref.stats["dropped"] == 0 and ref.stats["singleton_overrides"] == 0
     _assert_same(gpu, ref, f"reference build k={k}")
+
+
+@pytest.mark.parametrize("n_shards,k", [(2, 21), (3, 33), (8, 31), (4, 99)])
+def test_sharded_table_matches_oracle_shards(built, community, n_shards, k):
+    """N shards in one process on one GPU (local transport): reads split across shards, supermers routed to the owner
+    quick_hash(minimizer) % N (kmer_dht.cpp:192-196). Shard i must hold exactly the oracle's survivors with owner i."""
+    from mhm2_proxy_b200 import kcount
+    rb, ro = synth.make_reads(6000, community, error_rate=0.01, seed=500 + k, n_rate=1e-3)
+    cs, co, cd = synth.make_contigs(community, k, 40, seed=k + 7, depth_max=6)
+    ref = _oracle(k, rb, ro, num_shards=n_shards, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd)
+    n = len(ro) - 1
+    counters = [kcount.KmerCounter(k, num_shards=n_shards, shard_id=i, num_partitions=4, batch_reads=700) for i in range(n_shards)]
+    try:
+        for i, kc in enumerate(counters):
+            r0, r1 = n * i // n_shards, n * (i + 1) // n_shards
+            kc.add_reads(rb[int(ro[r0]):int(ro[r1])], ro[r0:r1 + 1] - ro[r0])
+            c0, c1 = len(cd) * i // n_shards, len(cd) * (i + 1) // n_shards
+            if c1 > c0:
+                kc.add_contigs(cs[int(co[c0]):int(co[c1])], co[c0:c1 + 1] - co[c0], cd[c0:c1])
+        kcount.finish_local_group(counters)
+        total = 0
+        for i, kc in enumerate(counters):
+            keys, counts, left, right = kc.survivors()
+            sel = ref.shard == i
+            assert np.array_equal(keys, ref.keys[sel]), f"shard {i}: key set differs ({len(keys)} vs {sel.sum()})"
+            assert np.array_equal(counts, ref.counts[sel]) and np.array_equal(left, ref.left[sel]) and np.array_equal(right, ref.right[sel])
+            total += len(keys)
+            st = kc.stats()
+            assert st["supermer_bytes_sent"] > 0
+        assert total == len(ref.keys)
+    finally:
+        for kc in counters:
+            kc.close()
+
+
+def test_nccl_exchange_two_gpus(built):
+    """Real NCCL transport, one process per GPU under torchrun (needs >= 2 GPUs: `gpurun --gpus 2`)."""
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(root, "tests", "nccl_worker.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "NCCL-PARITY-OK" in out.stdout
