@@ -151,7 +151,7 @@ def run_reference_arm(args):
     secs = sum(r["seconds"] for r in rates)
     v = inst / secs
     cb = dict(rates[-1]); cb["value"] = v
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup if args.ref_warm else 0, "ms_per_step": 1000 * secs / args.steps, "wall_s": wall,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
@@ -159,7 +159,7 @@ def run_reference_arm(args):
         "cpu_baseline": cb,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }))
+    })
 
 
 def workload_config(args, reads_per_gpu, n_gpus):
@@ -286,7 +286,7 @@ def run_ours(args):
                          "supermer_bytes": sk[0]["supermer_bytes_out"], "table_retries": sk[0]["table_retries"],
                          "table_group_bytes_max": sk[0]["table_bytes_max"],
                          "ms": {kk: round(sum(s[kk] for s in sk) / len(sk), 3) for kk in
-                                ("ms_parse_count", "ms_parse_fill", "ms_parse", "ms_clear", "ms_insert", "ms_filter", "ms_finish")},
+                                ("ms_parse_count", "ms_parse_fill", "ms_parse", "ms_exchange", "ms_clear", "ms_insert", "ms_filter", "ms_finish")},
                          "b_alg": round(b_alg(k), 2)}
     achieved = alg_bytes / (kern[dom] * 1e-3) / 1e9
     traffic = None
@@ -320,9 +320,21 @@ def run_ours(args):
         "kernel_ms": {k_: round(v, 3) for k_, v in kern.items()}, "per_k": per_k,
         "cpu_baseline": cpu, "clocks": clocks, "gen_s": round(t_gen, 1),
     }
-    print(json.dumps(out))
+    emit(out)
     if world > 1:
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, line)
+    else:
+        sys.stdout.write(line.decode())
 
 
 def main():
@@ -340,6 +352,11 @@ def main():
     ap.add_argument("--ref-warm", dest="ref_warm", action="store_true", help="also run warm-up passes in --impl reference")
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    # libraries (NCCL banner, torchrun notices) may write to fd 1: keep stdout for the ONE JSON line
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
     else:
