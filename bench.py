@@ -175,7 +175,7 @@ def one_pass(kcount, k, args, rank, world, dev, mode, tb, to, d_b, d_o, uid):
     n = to.numel() - 1
     inst_hint = n * (READ_LEN - k - 1)
     kc = kcount.KmerCounter(k, num_shards=world, shard_id=rank, device=dev, expected_instances=inst_hint,
-                            num_partitions=args.partitions, l2_table_mb=args.l2_mb)
+                            num_partitions=args.partitions)
     try:
         if world > 1:
             kc.comm_init(uid)
@@ -346,7 +346,6 @@ def main():
     ap.add_argument("--reads", type=int, default=C2_READS, help="reads per GPU")
     ap.add_argument("--ks", type=lambda s: tuple(int(x) for x in s.split(",")), default=C2_KS)
     ap.add_argument("--partitions", type=int, default=0)
-    ap.add_argument("--l2-mb", dest="l2_mb", type=int, default=0)
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=2)
     ap.add_argument("--ref-reads", dest="ref_reads", type=int, default=0, help="reads in the CPU sample (default 40k per core)")
     ap.add_argument("--ref-warm", dest="ref_warm", action="store_true", help="also run warm-up passes in --impl reference")

@@ -38,12 +38,14 @@ typedef struct kc_config {
   int32_t num_shards;        /* = upcxx::rank_n(): table is sharded by quick_hash(minimizer) % num_shards */
   int32_t shard_id;          /* = upcxx::rank_me(): which shard this handle owns */
   int32_t device;            /* CUDA device ordinal (reference: rank % ndev, gpu_utils.cpp:68-75) */
-  int32_t num_partitions;    /* 0 = auto. Power of two. L2-sized sub-tables per shard (internal, result-invariant) */
+  int32_t num_partitions;    /* 0 = auto. Sub-tables per shard, each sized to live in one CTA's shared memory while it is
+                                built (internal, result-invariant; all shards of a job must use the same value) */
   uint64_t expected_instances; /* hint: total k-mer instances this shard's caller will add (0 = size from first add);
                                   plays the role of estimate_num_kmers (contigging.cpp:61-91) */
   int32_t keep_prefilter;    /* 1 = also keep every distinct k-mer's counters after the reads pass (debug parity) */
   int32_t batch_reads;       /* 0 = auto. reads per internal batch (H2D copy / parse / exchange pipelining unit) */
-  int32_t l2_table_mb;       /* 0 = auto. budget for the group of partition tables processed together */
+  int32_t dbg_key_cap;       /* 0 = auto (what fits in shared memory). Upper bound on the distinct k-mers one shared-memory
+                                table holds; tests set it small to force the sub-pass path (result-invariant) */
   int32_t reserved[5];
 } kc_config;
 
@@ -61,17 +63,18 @@ typedef struct kc_stats {
   uint64_t distinct;            /* distinct canonical k-mers in this shard before the filter */
   uint64_t purged;              /* distinct - survivors */
   uint64_t survivors;
-  uint64_t dropped;             /* always 0: partition tables are re-run larger instead of dropping */
-  uint64_t table_retries;       /* partitions re-run with a larger table */
+  uint64_t dropped;             /* always 0: a partition that does not fit is re-run in sub-passes instead of dropping */
+  uint64_t table_retries;       /* work items re-run (split into sub-passes, or with wide counters) */
   uint64_t max_probe;
   uint64_t num_partitions;
   /* CUDA-event times on the library's own stream, summed over launches. ms_parse = parse_count + parse_fill kernels
-   * plus the bucket-layout round trip between them; ms_insert / ms_filter / ms_clear = those kernels only. */
+   * plus the bucket-layout round trip between them; ms_insert = the count kernel (insert + filter + compaction fused;
+   * ms_filter and ms_clear stay 0: the table lives in shared memory and is filtered where it was built). */
   double ms_h2d, ms_parse, ms_exchange, ms_insert, ms_filter, ms_total;
   double ms_parse_count, ms_parse_fill, ms_clear, ms_finish;
   uint64_t gpu_launches;        /* kernels launched by this handle so far */
   uint64_t n_parse_launches, n_insert_launches, n_filter_launches;
-  uint64_t table_bytes_max;     /* largest group of partition tables built at once (the L2-resident working set) */
+  uint64_t table_bytes_max;     /* shared memory per CTA of the count kernel (index table + key store + staging) */
   uint64_t reserved[4];
 } kc_stats;
 

@@ -46,6 +46,7 @@ struct Nccl;  // opaque, kc_comm.inl
 struct kc_handle {
   kc_config cfg;
   int KW = 1, m = 15, w = 1;
+  int smem_optin = 0, sms = 0;
   u32 P = 0;  // partitions per shard (0 until the first add decides)
   bool finished = false, has_ctg = false;
   cudaStream_t s_main = nullptr, s_copy = nullptr;
@@ -144,8 +145,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   if (cfg->dmin_thres < 1) return fail(h, KC_ERR_INVALID, "dmin_thres must be >= 1");
   if (cfg->num_shards < 1 || cfg->shard_id < 0 || cfg->shard_id >= cfg->num_shards)
     return fail(h, KC_ERR_INVALID, "bad shard %d of %d", cfg->shard_id, cfg->num_shards);
-  if (cfg->num_partitions && (cfg->num_partitions & (cfg->num_partitions - 1)))
-    return fail(h, KC_ERR_INVALID, "num_partitions must be a power of two");
+  if (cfg->num_partitions < 0 || cfg->num_partitions > (1 << 20)) return fail(h, KC_ERR_INVALID, "num_partitions outside 0..2^20");
   h->KW = k / 32 + 1;  // main.cpp:170, kmer.hpp:64
   int m = k * 2 / 3 + 1;  // kmer_dht.cpp:113-116
   if (m < 15) m = 15;
@@ -157,6 +157,8 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   CK(cudaGetDeviceCount(&ndev));
   if (cfg->device < 0 || cfg->device >= ndev) return fail(h, KC_ERR_INVALID, "device %d of %d", cfg->device, ndev);
   CK(cudaSetDevice(cfg->device));
+  CK(cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, cfg->device));
+  CK(cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, cfg->device));
   CK(cudaStreamCreateWithFlags(&h->s_main, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
   CK(cudaEventCreate(&h->ev_a));
@@ -174,19 +176,36 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
 
 namespace {
 
+// shared-memory table geometry of the count stage for this handle (kc_count.cuh): how many distinct k-mers one work item holds
+void table_geometry(const kc_handle *h, bool wide, bool ctg, u32 &tab_size, u32 &key_cap) {
+  const int KW = h->KW, VW = (wide ? VR_WIDE : VR_NARROW) + (ctg ? V_CTG : 0);
+  const size_t budget = (size_t)h->smem_optin - 2048;  // static shared memory + alignment slack
+  const size_t fixed = count_smem_bytes(KW, VW, 0, 0, ctg) + 8;
+  const size_t per_key = (size_t)KW * 8 + (size_t)VW * 4 + 8;  // + two 4-byte index-table entries (load <= 0.5)
+  u64 cap = budget > fixed ? (budget - fixed) / per_key : 16;
+  cap = std::min<u64>(cap, IDX_MASK - 1);
+  if (h->cfg.dbg_key_cap > 0) cap = std::min<u64>(cap, (u64)h->cfg.dbg_key_cap);
+  cap = std::max<u64>(cap, 16);
+  key_cap = (u32)cap;
+  tab_size = (u32)((2 * cap + 3) & ~3ull);
+}
+
 void decide_partitions(kc_handle *h, u64 inst_estimate) {
   if (h->P) return;
   if (h->cfg.num_partitions) {
     h->P = (u32)h->cfg.num_partitions;
   } else {
     u64 est = h->cfg.expected_instances ? h->cfg.expected_instances : inst_estimate;
-    // ~512K instances per partition keeps a partition's table (tens of thousands to ~100K distinct keys) at a few MB,
-    // so that a group of them is resident in the 126 MB L2 while it is being built
-    u64 want = (est + (512u << 10) - 1) / (512u << 10);
-    u32 p = next_pow2(std::max<u64>(want, 1));
-    h->P = std::min<u32>(p, 8192u);
+    // a partition should hold about 0.8 x key_cap distinct k-mers so that its whole table sits in one CTA's shared memory.
+    // distinct / instances is not known before counting: assume 0.25 (33x coverage with 0.5 % errors gives 0.13-0.19);
+    // a partition that turns out larger is re-run in sub-passes, never dropped.
+    u32 tab, cap;
+    table_geometry(h, false, false, tab, cap);
+    const double distinct = (double)est * 0.25;
+    u64 want = (u64)(distinct / (0.8 * cap)) + 1;
+    h->P = (u32)std::min<u64>(std::max<u64>(want, 1), 1u << 20);
   }
-  while ((u64)h->P * (u64)h->cfg.num_shards > 65536ull) h->P >>= 1;  // bucket ids are u16 inside the parse kernel
+  while ((u64)h->P * (u64)h->cfg.num_shards > (1ull << 22)) h->P >>= 1;
   // NOTE multi-shard: every shard must arrive at the same P (checked at exchange time); give all shards the same
   // cfg.num_partitions or cfg.expected_instances.
   h->st.num_partitions = h->P;
@@ -220,7 +239,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   a.max_len = (std::max(max_len, 32) + 31) & ~31;
   a.nsb = a.max_len / 16 + 4;
   a.nsv = a.max_len / 32 + 2;
-  a.smem_per_warp = (a.max_len * 8 + (a.nsb + 2 * a.nsv) * 4 + a.max_len * 2 + 15) & ~15;
+  a.smem_per_warp = (a.max_len * 8 + (a.nsb + 2 * a.nsv) * 4 + a.max_len * 4 + 15) & ~15;
   a.instances = (u64 *)h->d_misc.p;
   a.err = (u32 *)((char *)h->d_misc.p + 8);
   int warps = PARSE_THREADS / 32;
@@ -476,52 +495,25 @@ extern "C" int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *of
 
 namespace {
 
-struct PartWork {
-  u64 inst = 0, sup = 0;
-  u32 cap = 0;
-};
-
-template <int KW, bool CTG>
-int launch_group(kc_handle *h, const PartDesc *d_parts, const SegDesc *d_segs, int G, u32 max_chunks, u32 max_cap, const FilterArgs &fa_in,
-                 u32 *d_overflow, u32 *d_max_probe, cudaEvent_t *ev3) {
-  InsertArgs ia;
-  ia.parts = d_parts;
-  ia.segs = d_segs;
-  ia.k = h->cfg.kmer_len;
-  ia.overflow = d_overflow;
-  ia.max_probe = d_max_probe;
-  int sms = 148;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->cfg.device);
-  const u32 resident = (u32)sms * (2048 / INS_THREADS);
-  u32 gx = std::max<u32>(1, std::min<u32>(max_chunks, (2 * resident + G - 1) / G));
-  CK(cudaEventRecord(ev3[0], h->s_main));
-  insert_kernel<KW, CTG><<<dim3(gx, G), INS_THREADS, 0, h->s_main>>>(ia);
+template <int KW, bool WIDE, bool CTG>
+int launch_count(kc_handle *h, const CountArgs &ca, size_t smem, unsigned grid) {
+  CK(cudaFuncSetAttribute(count_kernel<KW, WIDE, CTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  count_kernel<KW, WIDE, CTG><<<grid, CNT_THREADS, smem, h->s_main>>>(ca);
   CK(cudaGetLastError());
-  CK(cudaEventRecord(ev3[1], h->s_main));
-  FilterArgs fa = fa_in;
-  fa.parts = d_parts;
-  u32 fx = std::max<u32>(1, std::min<u32>(max_cap / 256, (2 * resident + G - 1) / G));
-  filter_kernel<KW, CTG><<<dim3(fx, G), 256, 0, h->s_main>>>(fa);
-  CK(cudaGetLastError());
-  CK(cudaEventRecord(ev3[2], h->s_main));
-  h->st.gpu_launches += 2;
-  h->st.n_insert_launches++;
-  h->st.n_filter_launches++;
   return KC_OK;
 }
 
-int dispatch_group(kc_handle *h, bool ctg, const PartDesc *d_parts, const SegDesc *d_segs, int G, u32 max_chunks, u32 max_cap,
-                   const FilterArgs &fa, u32 *d_overflow, u32 *d_max_probe, cudaEvent_t *ev3) {
-#define GO(KWv)                                                                                                        \
-  return ctg ? launch_group<KWv, true>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe, ev3)   \
-             : launch_group<KWv, false>(h, d_parts, d_segs, G, max_chunks, max_cap, fa, d_overflow, d_max_probe, ev3)
+int dispatch_count(kc_handle *h, bool wide, bool ctg, const CountArgs &ca, size_t smem, unsigned grid) {
+#define GO3(KWv)                                                                               \
+  return wide ? (ctg ? launch_count<KWv, true, true>(h, ca, smem, grid) : launch_count<KWv, true, false>(h, ca, smem, grid)) \
+              : (ctg ? launch_count<KWv, false, true>(h, ca, smem, grid) : launch_count<KWv, false, false>(h, ca, smem, grid))
   switch (h->KW) {
-    case 1: GO(1);
-    case 2: GO(2);
-    case 3: GO(3);
-    case 4: GO(4);
+    case 1: GO3(1);
+    case 2: GO3(2);
+    case 3: GO3(3);
+    case 4: GO3(4);
   }
-#undef GO
+#undef GO3
   return fail(h, KC_ERR_INVALID, "unsupported key width %d", h->KW);
 }
 
@@ -548,40 +540,48 @@ int finish_count(kc_handle *h) {
   const u32 P = h->P;
   const int KW = h->KW;
   const u32 me = (u32)h->cfg.shard_id;
-  // every run of supermers that belongs to this shard, per partition
-  struct Src {
-    const SupHdr *hdr;
-    const u32 *payload;
-    u32 nsup, ninst;
-    bool ctg;
-  };
-  std::vector<std::vector<Src>> srcs(P);
+  // every run of supermers that belongs to this shard, partition-major
+  std::vector<const Block *> blks;
+  std::vector<u32> first_bucket;
   bool any_ctg = false;
-  auto add_block = [&](const Block &b, u32 first_bucket) {
-    if (!b.tot_sup) return;
-    for (u32 p = 0; p < P; p++) {
-      const u32 bi = first_bucket + p;
-      if (!b.hist[bi].nsup) continue;
-      srcs[p].push_back({b.hdr + b.hdr_base[bi], b.payload + b.pay_base[bi], b.hist[bi].nsup, b.hist[bi].ninst, b.is_ctg});
-      any_ctg |= b.is_ctg;
+  for (auto &b : h->blocks)
+    if (b.tot_sup) { blks.push_back(&b); first_bucket.push_back(me * P); any_ctg |= b.is_ctg; }
+  for (auto &b : h->rblocks)
+    if (b.tot_sup) { blks.push_back(&b); first_bucket.push_back(0); any_ctg |= b.is_ctg; }
+  std::vector<SegDesc> hsegs;
+  std::vector<WorkItem> items;
+  u64 read_inst = 0, ctg_inst = 0, tot_sup = 0;
+  for (u32 p = 0; p < P; p++) {
+    WorkItem it;
+    memset(&it, 0, sizeof(it));
+    it.seg_begin = (u32)hsegs.size();
+    u64 nsup = 0;
+    for (size_t bi = 0; bi < blks.size(); bi++) {
+      const Block &b = *blks[bi];
+      const u32 bu = first_bucket[bi] + p;
+      if (!b.hist[bu].nsup) continue;
+      SegDesc sd;
+      sd.hdr = b.hdr + b.hdr_base[bu];
+      sd.payload = b.payload + b.pay_base[bu];
+      sd.nsup = b.hist[bu].nsup;
+      sd.is_ctg = b.is_ctg ? 1 : 0;
+      sd.sup0 = (u32)nsup;
+      sd.pad = 0;
+      nsup += sd.nsup;
+      (b.is_ctg ? ctg_inst : read_inst) += b.hist[bu].ninst;
+      hsegs.push_back(sd);
     }
-  };
-  for (auto &b : h->blocks) add_block(b, me * P);
-  for (auto &b : h->rblocks) add_block(b, 0);
-  const int VW = any_ctg ? VW_CTG : VW_READS;
-  const size_t slot_bytes = (size_t)KW * 8 + (size_t)VW * 4;
-
-  std::vector<PartWork> work(P);
-  u64 tot_inst = 0, read_inst = 0, ctg_inst = 0, tot_sup = 0;
-  for (u32 p = 0; p < P; p++)
-    for (auto &s : srcs[p]) {
-      work[p].inst += s.ninst;
-      work[p].sup += s.nsup;
-      (s.ctg ? ctg_inst : read_inst) += s.ninst;
-      tot_sup += s.nsup;
-    }
-  tot_inst = read_inst + ctg_inst;
-  h->st.instances_inserted = tot_inst;
+    if (!nsup) continue;
+    if (nsup > 0xFFFFFFF0ull) return fail(h, KC_ERR_INVALID, "partition %u holds too many supermers: use more partitions", p);
+    it.seg_end = (u32)hsegs.size();
+    it.nsup = (u32)nsup;
+    it.part = p;
+    it.sub = 0;
+    it.nsub = 1;
+    tot_sup += nsup;
+    items.push_back(it);
+  }
+  h->st.instances_inserted = read_inst + ctg_inst;
   h->st.ctg_instances_inserted = ctg_inst;
   h->st.supermers_in = tot_sup;
 
@@ -597,182 +597,107 @@ int finish_count(kc_handle *h) {
     RC(ensure(h, h->pf_keys, pf_cap * KW * 8));
     RC(ensure(h, h->pf_vals, pf_cap * 18));
   }
-  DevBuf d_counters, d_overflow, d_partd, d_tab;
-  RC(ensure(h, d_counters, 64));
-  RC(ensure(h, d_overflow, (size_t)P * 4 + 4));
-  RC(ensure(h, d_partd, (size_t)P * 8));
-  CK(cudaMemsetAsync(d_counters.p, 0, 64, h->s_main));
-  CK(cudaMemsetAsync(d_overflow.p, 0, (size_t)P * 4 + 4, h->s_main));
-  CK(cudaMemsetAsync(d_partd.p, 0, (size_t)P * 8, h->s_main));
-  u32 *d_max_probe = (u32 *)d_overflow.p + P;
+  DevBuf d_counters, d_segs, d_items, d_status;
+  RC(ensure(h, d_counters, 128));
+  CK(cudaMemsetAsync(d_counters.p, 0, 128, h->s_main));
+  RC(ensure(h, d_segs, hsegs.size() * sizeof(SegDesc) + 64));
+  if (!hsegs.empty()) CK(cudaMemcpyAsync(d_segs.p, hsegs.data(), hsegs.size() * sizeof(SegDesc), cudaMemcpyHostToDevice, h->s_main));
 
-  FilterArgs fa;
-  memset(&fa, 0, sizeof(fa));
-  fa.k = h->cfg.kmer_len;
-  fa.dmin_thres = h->cfg.dmin_thres;
-  fa.frac = 1.0 - h->cfg.dyn_min_depth;  // kcount_cpu.cpp:178, evaluated in fp64 exactly as the reference does
-  fa.overflow = (const u32 *)d_overflow.p;
-  fa.out_keys = (u64 *)h->out_keys.p;
-  fa.out_counts = (uint16_t *)h->out_counts.p;
-  fa.out_left = (char *)h->out_left.p;
-  fa.out_right = (char *)h->out_right.p;
-  fa.out_cap = out_cap;
-  fa.counters = (u64 *)d_counters.p;
-  fa.pf_keys = h->cfg.keep_prefilter ? (u64 *)h->pf_keys.p : nullptr;
-  fa.pf_vals = (uint16_t *)h->pf_vals.p;
-  fa.pf_cap = pf_cap;
-  fa.part_distinct = (u64 *)d_partd.p;
+  CountArgs ca;
+  memset(&ca, 0, sizeof(ca));
+  ca.segs = (const SegDesc *)d_segs.p;
+  ca.k = h->cfg.kmer_len;
+  ca.dmin_thres = h->cfg.dmin_thres;
+  ca.frac = 1.0 - h->cfg.dyn_min_depth;  // kcount_cpu.cpp:178, evaluated in fp64 exactly as the reference does
+  ca.out_keys = (u64 *)h->out_keys.p;
+  ca.out_counts = (uint16_t *)h->out_counts.p;
+  ca.out_left = (char *)h->out_left.p;
+  ca.out_right = (char *)h->out_right.p;
+  ca.out_cap = out_cap;
+  ca.counters = (u64 *)d_counters.p;
+  ca.next_item = (u32 *)((u64 *)d_counters.p + 8);
+  ca.pf_keys = h->cfg.keep_prefilter ? (u64 *)h->pf_keys.p : nullptr;
+  ca.pf_vals = (uint16_t *)h->pf_vals.p;
+  ca.pf_cap = pf_cap;
 
-  const size_t l2_budget = (size_t)(h->cfg.l2_table_mb > 0 ? h->cfg.l2_table_mb : 64) << 20;
-  const int GMAX = 64;
-  std::vector<u32> todo;
-  for (u32 p = 0; p < P; p++)
-    if (work[p].sup) todo.push_back(p);
-  double ratio = 1.0;  // distinct / instances, learned from the first group (first group is sized for the worst case)
-  std::vector<PartDesc> hparts;
-  std::vector<SegDesc> hsegs;
-  std::vector<u64> h_partd(P);
-  std::vector<u32> h_over(P + 1);
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
+  std::vector<ItemStatus> status;
+  std::vector<WorkItem> wide_items;
+  bool wide = false;
   int round = 0;
-  std::vector<cudaEvent_t> group_events;  // 4 per group: before clear, before insert, after insert, after filter
-  std::vector<DevBuf> desc_bufs;  // descriptor arrays of every round stay alive until the end (no reuse, no host syncs)
-  auto cap_for = [&](u32 p) {
-    u64 want = (u64)((double)work[p].inst * ratio / 0.5) + 1;
-    return std::max<u32>(256, next_pow2(want));
-  };
-  while (!todo.empty()) {
-    if (round > 0)
-      for (u32 p : todo) {
-        if ((u64)work[p].cap >= 8ull * next_pow2(work[p].inst + 1)) return fail(h, KC_ERR_CUDA, "partition table cannot grow further");
-        work[p].cap *= 4;  // retry after running out of probe slots
-      }
-    size_t nsegs_round = 0;
-    for (u32 p : todo) nsegs_round += srcs[p].size();
-    DevBuf rb_parts, rb_segs;
-    RC(ensure(h, rb_parts, todo.size() * sizeof(PartDesc)));
-    RC(ensure(h, rb_segs, nsegs_round * sizeof(SegDesc)));
-    desc_bufs.push_back(rb_parts);
-    desc_bufs.push_back(rb_segs);
-    size_t part_pos = 0, seg_pos = 0;
-    size_t pos = 0;
-    bool learned = (round > 0);
-    while (pos < todo.size()) {
-      // greedy group of partitions whose tables fit the L2 budget together
-      int G = 0;
-      size_t bytes = 0;
-      const int gmax = learned ? GMAX : 2;  // the first group only has to teach us distinct/instances
-      while (pos + G < todo.size() && G < gmax) {
-        const u32 p = todo[pos + G];
-        if (round == 0) work[p].cap = cap_for(p);
-        const size_t tb = (size_t)work[p].cap * slot_bytes;
-        if (G > 0 && bytes + tb > l2_budget) break;
-        bytes += tb;
-        G++;
-      }
-      RC(ensure(h, d_tab, bytes + 256));
-      size_t keys_total = 0;
-      for (int g = 0; g < G; g++) keys_total += (size_t)work[todo[pos + g]].cap * KW * 8;
-      size_t koff = 0, voff = 0;
-      u32 max_chunks = 0, max_cap = 0;
-      hparts.clear();
-      hsegs.clear();
-      for (int g = 0; g < G; g++) {
-        const u32 p = todo[pos + g];
-        PartDesc pd;
-        memset(&pd, 0, sizeof(pd));
-        pd.keys = (u64 *)((char *)d_tab.p + koff);
-        pd.vals = (u32 *)((char *)d_tab.p + keys_total + voff);
-        koff += (size_t)work[p].cap * KW * 8;
-        voff += (size_t)work[p].cap * VW * 4;
-        pd.cap_mask = work[p].cap - 1;
-        pd.part = p;
-        pd.seg_begin = (u32)(seg_pos + hsegs.size());
-        u32 chunk = 0;
-        for (auto &sr : srcs[p]) {
-          SegDesc sd;
-          sd.hdr = sr.hdr;
-          sd.payload = sr.payload;
-          sd.nsup = sr.nsup;
-          sd.is_ctg = sr.ctg ? 1 : 0;
-          sd.chunk0 = chunk;
-          sd.pad = 0;
-          chunk += (sr.nsup + CH - 1) / CH;
-          hsegs.push_back(sd);
-        }
-        pd.seg_end = (u32)(seg_pos + hsegs.size());
-        pd.nchunks = chunk;
-        max_chunks = std::max(max_chunks, chunk);
-        max_cap = std::max(max_cap, work[p].cap);
-        hparts.push_back(pd);
-      }
-      PartDesc *dp = (PartDesc *)rb_parts.p + part_pos;
-      SegDesc *ds = (SegDesc *)rb_segs.p;  // segments are indexed absolutely inside this round's array
-      CK(cudaMemcpyAsync(dp, hparts.data(), hparts.size() * sizeof(PartDesc), cudaMemcpyHostToDevice, h->s_main));
-      CK(cudaMemcpyAsync(ds + seg_pos, hsegs.data(), hsegs.size() * sizeof(SegDesc), cudaMemcpyHostToDevice, h->s_main));
-      part_pos += hparts.size();
-      seg_pos += hsegs.size();
-      cudaEvent_t ev4[4];
-      for (auto &e : ev4) {
-        CK(cudaEventCreate(&e));
-        group_events.push_back(e);
-      }
-      h->st.table_bytes_max = std::max<u64>(h->st.table_bytes_max, bytes);
-      CK(cudaEventRecord(ev4[0], h->s_main));
-      CK(cudaMemsetAsync(d_tab.p, 0xFF, keys_total, h->s_main));
-      CK(cudaMemsetAsync((char *)d_tab.p + keys_total, 0, bytes - keys_total, h->s_main));
-      int rc = dispatch_group(h, any_ctg, dp, ds, G, max_chunks, max_cap, fa, (u32 *)d_overflow.p, d_max_probe, ev4 + 1);
-      if (rc) return rc;
-      if (!learned) {  // learn distinct/instances from the first group, then size the rest for <= ~50% load with margin
-        CK(cudaMemcpyAsync(h_partd.data(), d_partd.p, (size_t)P * 8, cudaMemcpyDeviceToHost, h->s_main));
-        CK(cudaStreamSynchronize(h->s_main));
-        double r = 0;
-        for (int g = 0; g < G; g++) {
-          const u32 p = todo[pos + g];
-          if (work[p].inst) r = std::max(r, (double)h_partd[p] / (double)work[p].inst);
-        }
-        ratio = std::min(1.0, r * 1.3 + 0.01);
-        learned = true;
-      }
-      pos += G;
+  while (!items.empty() || !wide_items.empty()) {
+    if (items.empty()) {  // narrow rounds are done: re-run the items whose u16 counters wrapped with u32 counters
+      items.swap(wide_items);
+      wide = true;
     }
-    // which partitions ran out of probe slots?
-    CK(cudaMemcpyAsync(h_over.data(), d_overflow.p, (size_t)P * 4 + 4, cudaMemcpyDeviceToHost, h->s_main));
+    if (++round > 64) return fail(h, KC_ERR_CUDA, "count stage does not converge");
+    // heaviest first (longest-processing-time order for the dynamic scheduler)
+    std::stable_sort(items.begin(), items.end(), [](const WorkItem &a, const WorkItem &b) { return a.nsup > b.nsup; });
+    u32 tab_size, key_cap;
+    table_geometry(h, wide, any_ctg, tab_size, key_cap);
+    const int VW = (wide ? VR_WIDE : VR_NARROW) + (any_ctg ? V_CTG : 0);
+    const size_t smem = count_smem_bytes(KW, VW, tab_size, key_cap, any_ctg) + 8;
+    RC(ensure(h, d_items, items.size() * sizeof(WorkItem)));
+    RC(ensure(h, d_status, items.size() * sizeof(ItemStatus)));
+    CK(cudaMemcpyAsync(d_items.p, items.data(), items.size() * sizeof(WorkItem), cudaMemcpyHostToDevice, h->s_main));
+    CK(cudaMemsetAsync(ca.next_item, 0, 4, h->s_main));
+    ca.items = (const WorkItem *)d_items.p;
+    ca.status = (ItemStatus *)d_status.p;
+    ca.nitems = (u32)items.size();
+    ca.tab_size = tab_size;
+    ca.key_cap = key_cap;
+    const unsigned grid = (unsigned)std::min<size_t>(items.size(), (size_t)h->sms);
+    CK(cudaEventRecord(h->ev_c, h->s_main));
+    RC(dispatch_count(h, wide, any_ctg, ca, smem, grid));
+    CK(cudaEventRecord(h->ev_d, h->s_main));
+    h->st.gpu_launches++;
+    h->st.n_insert_launches++;
+    status.resize(items.size());
+    CK(cudaMemcpyAsync(status.data(), d_status.p, items.size() * sizeof(ItemStatus), cudaMemcpyDeviceToHost, h->s_main));
     CK(cudaStreamSynchronize(h->s_main));
-    std::vector<u32> again;
-    for (u32 p : todo)
-      if (h_over[p]) again.push_back(p);
-    h->st.max_probe = std::max<u64>(h->st.max_probe, h_over[P]);
-    if (!again.empty()) {
-      h->st.table_retries += again.size();
-      CK(cudaMemsetAsync(d_overflow.p, 0, (size_t)P * 4, h->s_main));
+    h->st.ms_insert += elapsed(h->ev_c, h->ev_d);
+    h->st.table_bytes_max = std::max<u64>(h->st.table_bytes_max, smem);
+    std::vector<WorkItem> again;
+    for (size_t i = 0; i < items.size(); i++) {
+      const WorkItem &it = items[i];
+      if (status[i].overflow) {
+        // it filled its key store after `progress` of `nsup` supermers: split its hash range so that each child should end
+        // up around 60 % full
+        const double frac_done = std::max(1.0, (double)status[i].progress) / (double)it.nsup;
+        u32 f = 2;
+        while (f < 256 && (double)f * frac_done < 1.6) f <<= 1;
+        if ((u64)it.nsub * f > (1u << 20)) return fail(h, KC_ERR_CUDA, "partition %u cannot be split further", it.part);
+        for (u32 c = 0; c < f; c++) {
+          WorkItem ch = it;
+          ch.sub = it.sub + c * it.nsub;
+          ch.nsub = it.nsub * f;
+          again.push_back(ch);
+        }
+        h->st.table_retries++;
+      } else if (status[i].wide) {
+        wide_items.push_back(it);
+        h->st.table_retries++;
+      }
     }
-    todo.swap(again);
-    round++;
+    items.swap(again);
   }
-  for (auto &b : desc_bufs) release(b);
   CK(cudaEventRecord(e1, h->s_main));
   u64 counters[8];
   CK(cudaMemcpyAsync(counters, d_counters.p, 64, cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
   h->st.ms_finish += elapsed(e0, e1);
-  for (size_t g = 0; g + 3 < group_events.size(); g += 4) {
-    h->st.ms_clear += elapsed(group_events[g], group_events[g + 1]);
-    h->st.ms_insert += elapsed(group_events[g + 1], group_events[g + 2]);
-    h->st.ms_filter += elapsed(group_events[g + 2], group_events[g + 3]);
-  }
-  for (auto e : group_events) cudaEventDestroy(e);
   release(d_counters);
-  release(d_overflow);
-  release(d_partd);
-  release(d_tab);
+  release(d_segs);
+  release(d_items);
+  release(d_status);
   if (counters[3]) return fail(h, KC_ERR_OVERFLOW, "survivor output capacity exceeded");
   h->n_surv = counters[0];
   h->n_pf = counters[1];
   h->st.distinct = counters[2];
   h->st.survivors = counters[0];
   h->st.purged = counters[2] - counters[0];
+  h->st.max_probe = counters[4];
   u64 inst_parsed = 0;
   CK(cudaMemcpy(&inst_parsed, h->d_misc.p, 8, cudaMemcpyDeviceToHost));
   h->st.instances_parsed = inst_parsed;

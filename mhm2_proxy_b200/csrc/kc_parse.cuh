@@ -6,8 +6,8 @@
 //      (high quality AND one of ACGT: kcount.cpp:81-84, kcount_cpu.cpp:157-164,320-323), packed with REDUX/ballot;
 //   2. canonical m-mer of every position (min(fwd, revcomp), left-aligned u64);
 //   3. sliding-window MAX over k-m+1 positions by in-place doubling in shared memory = the minimizer of every k-mer;
-//   4. bucket = (quick_hash(minimizer) % num_shards, partition bits of the same hash); supermer = maximal run of
-//      equal buckets over k-mers 1..len-k-1 (first and last k-mer are never counted, kcount_cpu.cpp:84-102);
+//   4. bucket = (quick_hash(minimizer) % num_shards, partition from the high half of the same hash); supermer = maximal
+//      run (<= 64 k-mers) of equal buckets over k-mers 1..len-k-1 (first and last k-mer are never counted, kcount_cpu.cpp:84-102);
 //   5. one lane per supermer appends {header, 2-bit bases, valid bits} to its bucket.
 // The kernel runs twice per batch: COUNT (bucket histogram only) then FILL (exact-size buckets, no overflow possible).
 #pragma once
@@ -37,7 +37,7 @@ struct ParseArgs {
   int ascii;               // 0: PackedRead bytes (base | qual<<3), 1: ASCII ACGTN (contigs)
   int k, m, w;             // k-mer length, minimizer length, window = k-m+1
   int qual_cutoff;
-  u32 num_shards, num_parts;  // num_parts is a power of two
+  u32 num_shards, num_parts;  // partitions per shard (any number >= 1)
   int max_len;             // multiple of 32, >= every sequence length in this launch
   int nsb, nsv;            // shared words for bases / valid bits per warp
   int smem_per_warp;
@@ -56,11 +56,12 @@ __device__ __forceinline__ u32 bucket_of(u64 minimizer, u32 num_shards, u32 num_
   if (num_shards == 1) shard = 0;
   else if ((num_shards & (num_shards - 1)) == 0) shard = (u32)qh & (num_shards - 1);
   else shard = (u32)(qh % num_shards);                 // kmer_dht.cpp:195
-  const u32 part = (u32)(qh >> 32) & (num_parts - 1);  // internal: which L2-sized sub-table of that shard
+  const u32 part = __umulhi((u32)(qh >> 32), num_parts);  // internal: which shared-memory-sized sub-table of that shard
   return shard * num_parts + part;
 }
 
 constexpr int PARSE_THREADS = 256;
+constexpr int SUP_MAX_KMERS = 64;  // longest supermer, in k-mers (supermer boundaries are free to differ from the reference's)
 
 template <bool FILL>
 __global__ void __launch_bounds__(PARSE_THREADS) parse_kernel(const ParseArgs a) {
@@ -71,7 +72,7 @@ __global__ void __launch_bounds__(PARSE_THREADS) parse_kernel(const ParseArgs a)
   u32 *sb = (u32 *)(c + a.max_len);     // [nsb] 2-bit bases, 16 per word, MSB first
   u32 *sv = sb + a.nsb;                 // [nsv] valid bits, LSB first
   u32 *st = sv + a.nsv;                 // [nsv] supermer-start bits over k-mers 1..nk (bit t of word j <-> k-mer 1+32j+t)
-  uint16_t *bk = (uint16_t *)(st + a.nsv);  // [max_len] bucket of k-mer i
+  u32 *bk = st + a.nsv;                 // [max_len] bucket of k-mer i
   const unsigned FULL = 0xffffffffu;
   u64 local_inst = 0;
   const int k = a.k, m = a.m, w = a.w;
@@ -153,11 +154,12 @@ __global__ void __launch_bounds__(PARSE_THREADS) parse_kernel(const ParseArgs a)
       if (i <= nk) {
         const u64 v1 = c[i], v2 = c[i + w - span];
         b = bucket_of(v1 > v2 ? v1 : v2, a.num_shards, a.num_parts);
-        bk[i] = (uint16_t)b;
+        bk[i] = b;
       }
       u32 pb = __shfl_up_sync(FULL, b, 1);
       if (lane == 0) pb = carry;
-      const u32 sm = __ballot_sync(FULL, (i <= nk) && (b != pb));
+      // a supermer also ends after SUP_MAX_KMERS k-mers (the count stage indexes k-mers inside a supermer with 6 bits)
+      const u32 sm = __ballot_sync(FULL, (i <= nk) && ((b != pb) || ((i - 1) & (SUP_MAX_KMERS - 1)) == 0));
       if (lane == 0) st[j0 >> 5] = sm;
       carry = __shfl_sync(FULL, b, 31);
     }

@@ -20,7 +20,7 @@ class KcConfig(C.Structure):
         ("kmer_len", C.c_int32), ("qual_cutoff", C.c_int32), ("dmin_thres", C.c_int32), ("dyn_min_depth", C.c_double),
         ("num_shards", C.c_int32), ("shard_id", C.c_int32), ("device", C.c_int32), ("num_partitions", C.c_int32),
         ("expected_instances", C.c_uint64), ("keep_prefilter", C.c_int32), ("batch_reads", C.c_int32),
-        ("l2_table_mb", C.c_int32), ("reserved", C.c_int32 * 5),
+        ("dbg_key_cap", C.c_int32), ("reserved", C.c_int32 * 5),
     ]
 
 
@@ -93,13 +93,13 @@ class KmerCounter:
     add_reads* -> [add_contigs] -> finish -> survivors."""
 
     def __init__(self, kmer_len, dmin_thres=2, num_shards=1, shard_id=0, device=0, num_partitions=0, expected_instances=0,
-                 keep_prefilter=False, batch_reads=0, l2_table_mb=0, qual_cutoff=20, dyn_min_depth=0.9):
+                 keep_prefilter=False, batch_reads=0, dbg_key_cap=0, qual_cutoff=20, dyn_min_depth=0.9):
         self.lib = load_library()
         cfg = KcConfig()
         self.lib.kc_config_default(C.byref(cfg), kmer_len)
         cfg.dmin_thres, cfg.num_shards, cfg.shard_id, cfg.device = dmin_thres, num_shards, shard_id, device
         cfg.num_partitions, cfg.expected_instances = num_partitions, expected_instances
-        cfg.keep_prefilter, cfg.batch_reads, cfg.l2_table_mb = int(keep_prefilter), batch_reads, l2_table_mb
+        cfg.keep_prefilter, cfg.batch_reads, cfg.dbg_key_cap = int(keep_prefilter), batch_reads, dbg_key_cap
         cfg.qual_cutoff, cfg.dyn_min_depth = qual_cutoff, dyn_min_depth
         self.k = kmer_len
         self.n_longs = kmer_len // 32 + 1

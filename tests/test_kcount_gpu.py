@@ -85,6 +85,28 @@ def test_reads_parity(built, community, k, parts):
     assert st["dropped"] == 0
 
 
+@pytest.mark.parametrize("k,cap", [(21, 48), (33, 200), (99, 1000)])
+def test_subpass_split_parity(built, community, k, cap):
+    """A partition with more distinct k-mers than one shared-memory table holds is re-run as hash sub-passes
+    (dbg_key_cap forces that path hard: every partition is split many times); results must not change."""
+    rb, ro = synth.make_reads(3000, community, error_rate=0.01, seed=31 + k, n_rate=1e-3)
+    cs, co, cd = synth.make_contigs(community, k, 30, seed=k + 3, depth_max=6)
+    gpu = _gpu(k, rb, ro, num_partitions=3, dbg_key_cap=cap, keep_prefilter=True, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd)
+    ref = _oracle(k, rb, ro, want_prefilter=True, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd)
+    _assert_same(gpu, ref, f"sub-pass k={k}")
+    assert gpu[4]["table_retries"] > 0
+    assert np.array_equal(gpu[5][0], ref.pf_keys) and np.array_equal(gpu[5][1], ref.pf_vals)
+
+
+def test_auto_partitions(built, community):
+    """num_partitions=0: the library sizes the partitions itself (non-power-of-two counts included)."""
+    k = 31
+    rb, ro = synth.make_reads(20000, community, error_rate=0.01, seed=77)
+    for parts in (0, 5, 37, 1000):
+        gpu = _gpu(k, rb, ro, num_partitions=parts)
+        _assert_same(gpu, _oracle(k, rb, ro), f"parts={parts}")
+
+
 @pytest.mark.parametrize("k", [21, 33, 99])
 def test_ragged_reads_parity(built, community, k):
     rb, ro = synth.make_reads(6000, community, read_len=180, error_rate=0.02, seed=7 + k, n_rate=1e-3, var_len=True)
@@ -153,6 +175,7 @@ def test_saturation_and_heavy_hitters(built):
     assert ref.pf_vals.max() == 65535
     _assert_same(gpu, ref, "saturation")
     assert np.array_equal(gpu[5][1], ref.pf_vals)
+    assert gpu[4]["table_retries"] > 0  # the u16 counters wrapped: those work items were re-run with u32 counters
 
 
 def test_edge_cases(built, community):
