@@ -85,6 +85,9 @@ int kc_create(const kc_config *cfg, kc_handle **out);
 /* ~KmerDHT / ~HashTableInserter (kmer_dht.cpp:161-166, kcount_cpu.cpp:417-423) */
 int kc_destroy(kc_handle *h);
 const char *kc_last_error(const kc_handle *h);
+/* Device buffers freed by a handle are cached per process for the next kcount round (one round per k, main.cpp:169);
+ * this returns them to the driver (e.g. before the alignment stage needs the GPU memory). */
+int kc_release_cached_memory(void);
 
 /* count_kmers' read loop -> SeqBlockInserter::process_seq(seq, 0) (kcount.cpp:72-88, kcount_cpu.cpp:73-103).
  * bytes = PackedRead bytes verbatim (packed_reads.cpp:73-109: base 0..4 | min(qual,31) << 3), offsets[n_reads+1].
@@ -96,6 +99,13 @@ int kc_add_reads_device(kc_handle *h, const uint8_t *d_bytes, const uint64_t *d_
 /* add_ctg_kmers' loop -> process_seq(ctg.seq, ctg.get_uint16_t_depth()) (kcount.cpp:123-130, contigs.hpp:57-66).
  * seqs = ASCII ACGTN (host), offsets[n+1], depths = Contig::depth doubles. Any length; long contigs are tiled. */
 int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs);
+/* reads in the form count_kmers hands them to SeqBlockInserter::process_seq(seq, 0) (kcount.cpp:81-86): ASCII ACGTN with
+ * LOWER CASE = quality below the cut-off. Used by the pimpl binding (integration/kcount_b200.cpp); kc_add_reads, which
+ * takes the PackedRead bytes directly, is the fast path. */
+int kc_add_reads_ascii(kc_handle *h, const char *seqs, const uint64_t *offsets, uint64_t n_reads);
+/* the global _dmin_thres (kmer_dht.hpp:57) is assigned by analyze_kmers AFTER the KmerDHT / HashTableInserter exist
+ * (kcount.cpp:145): set it any time before kc_finish */
+int kc_set_dmin_thres(kc_handle *h, int32_t dmin_thres);
 
 /* multi-GPU: bind an NCCL communicator built from a 128-byte ncclUniqueId shared by all shards
  * (replaces ThreeTierAggrStore<Supermer> / rpc_ff, kmer_dht.cpp:133,146-149,222-231). Not needed when num_shards==1. */

@@ -9,6 +9,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 #include <dlfcn.h>
@@ -21,7 +23,7 @@ using namespace kc;
 
 namespace {
 
-constexpr int SEG_MAX = 1024;  // longest sequence a parse warp handles in one piece; longer ones are tiled with k+1 overlap
+constexpr int SEG_MAX = PARSE_TILE;  // longest sequence a parse thread handles in one piece; longer ones are tiled with k+1 overlap
 
 struct DevBuf {
   void *p = nullptr;
@@ -53,6 +55,7 @@ struct kc_handle {
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
   std::vector<Block> blocks;       // produced locally
   std::vector<Block> rblocks;      // received from peers (multi-shard)
+  std::vector<BucketBase> h_base;  // staging for the per-batch bucket layout
   DevBuf stage_bytes[2], stage_offs[2];
   DevBuf d_hist, d_cursor, d_hdr_base, d_pay_base, d_misc;  // d_misc: u64 instances, u32 err
   // outputs
@@ -89,19 +92,83 @@ int fail(kc_handle *h, int code, const char *fmt, ...) {
     if (r_) return r_;      \
   } while (0)
 
+// Process-wide caching device allocator. A job runs one kcount round per k (main.cpp:169) and every round needs the same
+// multi-GB buffers (supermer buckets, survivor arrays); cudaMalloc/cudaFree of those costs tens of milliseconds per round,
+// so freed blocks are kept per device and handed out again. Rule kept by every caller in this file: a block is freed only
+// after the stream work that used it has been synchronised. kc_release_cached_memory() gives the memory back.
+struct DevCache {
+  std::mutex mu;
+  std::map<int, std::multimap<size_t, void *>> free_blocks;  // device -> size -> block
+  std::map<void *, std::pair<int, size_t>> live;             // block -> (device, size)
+};
+DevCache &dev_cache() {
+  static DevCache c;
+  return c;
+}
+
+cudaError_t dev_alloc(void **p, size_t bytes) {
+  *p = nullptr;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  bytes = (bytes + 511) & ~(size_t)511;
+  DevCache &c = dev_cache();
+  {
+    std::lock_guard<std::mutex> lk(c.mu);
+    auto &fb = c.free_blocks[dev];
+    auto it = fb.lower_bound(bytes);
+    if (it != fb.end() && it->first <= bytes + bytes / 2 + (1u << 20)) {
+      *p = it->second;
+      c.live[*p] = {dev, it->first};
+      fb.erase(it);
+      return cudaSuccess;
+    }
+  }
+  e = cudaMalloc(p, bytes);
+  if (e == cudaErrorMemoryAllocation) {  // give the cached blocks of this device back and try again
+    cudaGetLastError();
+    std::vector<void *> drop;
+    {
+      std::lock_guard<std::mutex> lk(c.mu);
+      for (auto &kv : c.free_blocks[dev]) drop.push_back(kv.second);
+      c.free_blocks[dev].clear();
+    }
+    for (void *q : drop) cudaFree(q);
+    e = cudaMalloc(p, bytes);
+  }
+  if (e == cudaSuccess) {
+    std::lock_guard<std::mutex> lk(c.mu);
+    c.live[*p] = {dev, bytes};
+  }
+  return e;
+}
+
+void dev_free(void *p) {
+  if (!p) return;
+  DevCache &c = dev_cache();
+  std::lock_guard<std::mutex> lk(c.mu);
+  auto it = c.live.find(p);
+  if (it == c.live.end()) {
+    cudaFree(p);
+    return;
+  }
+  c.free_blocks[it->second.first].emplace(it->second.second, p);
+  c.live.erase(it);
+}
+
 int ensure(kc_handle *h, DevBuf &b, size_t bytes) {
   if (b.bytes >= bytes && b.p) return KC_OK;
-  if (b.p) CK(cudaFree(b.p));
+  if (b.p) dev_free(b.p);
   b.p = nullptr;
   b.bytes = 0;
   size_t want = bytes + bytes / 8 + 256;
-  CK(cudaMalloc(&b.p, want));
+  CK(dev_alloc(&b.p, want));
   b.bytes = want;
   return KC_OK;
 }
 
 void release(DevBuf &b) {
-  if (b.p) cudaFree(b.p);
+  if (b.p) dev_free(b.p);
   b.p = nullptr;
   b.bytes = 0;
 }
@@ -219,8 +286,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   const u32 NP = h->P * (u32)h->cfg.num_shards;
   RC(ensure(h, h->d_hist, sizeof(BucketHist) * NP));
   RC(ensure(h, h->d_cursor, sizeof(BucketHist) * NP));
-  RC(ensure(h, h->d_hdr_base, sizeof(u64) * NP));
-  RC(ensure(h, h->d_pay_base, sizeof(u64) * NP));
+  RC(ensure(h, h->d_hdr_base, sizeof(BucketBase) * NP));
   ParseArgs a;
   memset(&a, 0, sizeof(a));
   a.bytes = d_bytes;
@@ -233,35 +299,34 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   a.k = h->cfg.kmer_len;
   a.m = h->m;
   a.w = h->w;
-  a.qual_cutoff = h->cfg.qual_cutoff;
+  const u32 cutoff = (u32)std::min(std::max(h->cfg.qual_cutoff, 0), 64);
+  a.qual_add = (0x80u - cutoff) * 0x01010101u;
   a.num_shards = (u32)h->cfg.num_shards;
   a.num_parts = h->P;
-  a.max_len = (std::max(max_len, 32) + 31) & ~31;
-  a.nsb = a.max_len / 16 + 4;
-  a.nsv = a.max_len / 32 + 2;
-  a.smem_per_warp = (a.max_len * 8 + (a.nsb + 2 * a.nsv) * 4 + a.max_len * 4 + 15) & ~15;
+  if (max_len > PARSE_TILE) return fail(h, KC_ERR_INVALID, "internal: sequence of %d bases reached a parse thread", max_len);
+  const int n16 = (15 + std::max(max_len, 16) + 15) >> 4;  // 16-byte chunks of the longest sequence at the worst alignment
+  a.nsb = n16 + 4;
+  a.nsv = (n16 + 1) / 2 + 2;
   a.instances = (u64 *)h->d_misc.p;
   a.err = (u32 *)((char *)h->d_misc.p + 8);
-  int warps = PARSE_THREADS / 32;
-  while (warps > 1 && (size_t)warps * a.smem_per_warp > 200u * 1024u) warps >>= 1;
-  const size_t smem = (size_t)warps * a.smem_per_warp;
-  if (smem > 220u * 1024u) return fail(h, KC_ERR_INVALID, "sequence too long for one parse warp: %d", max_len);
+  const int words_per_thread = a.nsb + a.nsv + 2 * a.w + PARSE_LCAP / 2;
+  int threads = PARSE_THREADS;
+  while (threads > 32 && (size_t)threads * words_per_thread * 4 > 96u * 1024u) threads >>= 1;
+  const size_t smem = (size_t)threads * words_per_thread * 4;
   CK(cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   CK(cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int dev_sms = 148;
-  cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, h->cfg.device);
   int per_sm = 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, parse_kernel<true>, warps * 32, smem));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, parse_kernel<true>, threads, smem));
   per_sm = std::max(per_sm, 1);
-  u64 need_blocks = (nseq + warps - 1) / warps;
-  const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)dev_sms * per_sm * 4);
+  const u64 need_blocks = (nseq + threads - 1) / threads;
+  const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * per_sm * 2);
 
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
   // COUNT
   CK(cudaMemsetAsync(h->d_hist.p, 0, sizeof(BucketHist) * NP, h->s_main));
   a.hist = (BucketHist *)h->d_hist.p;
-  parse_kernel<false><<<grid, warps * 32, smem, h->s_main>>>(a);
+  parse_kernel<false><<<grid, threads, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
@@ -288,20 +353,20 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
     CK(cudaEventRecord(e1, h->s_main));
     return KC_OK;
   }
-  CK(cudaMalloc((void **)&blk.hdr, sizeof(SupHdr) * (hs + 1)));
-  CK(cudaMalloc((void **)&blk.payload, sizeof(u32) * (ps + 8)));  // + slack: fetch64 may read 2 words past a record
+  CK(dev_alloc((void **)&blk.hdr, sizeof(SupHdr) * (hs + 1)));
+  CK(dev_alloc((void **)&blk.payload, sizeof(u32) * (ps + 8)));  // + slack: fetch64 may read 2 words past a record
   CK(cudaMemsetAsync(blk.payload + ps, 0, sizeof(u32) * 8, h->s_main));
-  CK(cudaMemcpyAsync(h->d_hdr_base.p, blk.hdr_base.data(), sizeof(u64) * NP, cudaMemcpyHostToDevice, h->s_main));
-  CK(cudaMemcpyAsync(h->d_pay_base.p, blk.pay_base.data(), sizeof(u64) * NP, cudaMemcpyHostToDevice, h->s_main));
+  h->h_base.resize(NP);
+  for (u32 b = 0; b < NP; b++) h->h_base[b] = BucketBase{blk.hdr_base[b], blk.pay_base[b]};
+  CK(cudaMemcpyAsync(h->d_hdr_base.p, h->h_base.data(), sizeof(BucketBase) * NP, cudaMemcpyHostToDevice, h->s_main));
   CK(cudaMemsetAsync(h->d_cursor.p, 0, sizeof(BucketHist) * NP, h->s_main));
   // FILL
   a.hist = (BucketHist *)h->d_cursor.p;
-  a.hdr_base = (const u64 *)h->d_hdr_base.p;
-  a.pay_base = (const u64 *)h->d_pay_base.p;
+  a.base = (const BucketBase *)h->d_hdr_base.p;
   a.hdr = blk.hdr;
   a.payload = blk.payload;
   CK(cudaEventRecord(h->ev_d, h->s_main));
-  parse_kernel<true><<<grid, warps * 32, smem, h->s_main>>>(a);
+  parse_kernel<true><<<grid, threads, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
@@ -453,43 +518,76 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
   return KC_OK;
 }
 
-extern "C" int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs) {
+namespace {
+
+// ASCII sequences (ACGTN, lower case = low quality): contigs with their depths, or reads as count_kmers hands them to
+// process_seq (kcount.cpp:81-86). Any length; sequences longer than one parse thread's tile are cut with k+1 overlap.
+int add_ascii(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_seqs, bool is_ctg) {
   if (!h) return KC_ERR_INVALID;
   if (h->finished) return fail(h, KC_ERR_STATE, "add after finish");
-  if (n_ctgs == 0) return KC_OK;
-  if (!seqs || !offsets || !depths) return fail(h, KC_ERR_INVALID, "null input");
+  if (n_seqs == 0) return KC_OK;
+  if (!seqs || !offsets || (is_ctg && !depths)) return fail(h, KC_ERR_INVALID, "null input");
   CK(cudaSetDevice(h->cfg.device));
   const int k = h->cfg.kmer_len;
   std::vector<u64> ss;
   std::vector<u32> sl;
   std::vector<uint16_t> sd;
   u64 inst = 0;
-  const int tile = std::min(SEG_MAX, std::max(512, 4 * (k + 2)));
-  for (u64 c = 0; c < n_ctgs; c++) {
+  for (u64 c = 0; c < n_seqs; c++) {
     const u64 len = offsets[c + 1] - offsets[c];
     if (len < (u64)k + 2) continue;  // kcount.cpp:126
-    const double d = depths[c];
-    uint16_t depth = (uint16_t)(d > 65535 ? 65535 : d);  // contigs.hpp:57-66 get_uint16_t_depth
-    if (!depth) depth = 1;                               // kcount_cpu.cpp:75
+    uint16_t depth = 1;
+    if (is_ctg) {
+      const double d = depths[c];
+      depth = (uint16_t)(d > 65535 ? 65535 : d);  // contigs.hpp:57-66 get_uint16_t_depth
+      if (!depth) depth = 1;                       // kcount_cpu.cpp:75
+    }
     inst += len - k - 1;
-    tile_sequence(offsets[c], len, k, tile, depth, ss, sl, sd);
+    tile_sequence(offsets[c], len, k, SEG_MAX, depth, ss, sl, sd);
   }
   decide_partitions(h, inst);
   if (ss.empty()) return KC_OK;
-  const u64 b0 = offsets[0], b1 = offsets[n_ctgs];
+  const u64 b0 = offsets[0], b1 = offsets[n_seqs];
   DevBuf d_seq;
   int rc = ensure(h, d_seq, b1 - b0 + 64);
   if (rc) return rc;
   CK(cudaMemcpyAsync(d_seq.p, seqs + b0, b1 - b0, cudaMemcpyHostToDevice, h->s_main));
-  rc = parse_segments(h, (const uint8_t *)d_seq.p - b0, ss, sl, sd, tile, true, true);
+  // segments are parsed in slices so that the per-batch bucket buffers stay bounded
+  const size_t SLICE = 4u << 20;
+  for (size_t s0 = 0; s0 < ss.size() && !rc; s0 += SLICE) {
+    const size_t s1 = std::min(ss.size(), s0 + SLICE);
+    std::vector<u64> a(ss.begin() + s0, ss.begin() + s1);
+    std::vector<u32> b(sl.begin() + s0, sl.begin() + s1);
+    std::vector<uint16_t> c(sd.begin() + s0, sd.begin() + s1);
+    rc = parse_segments(h, (const uint8_t *)d_seq.p - b0, a, b, c, SEG_MAX, true, is_ctg);
+  }
+  CK(cudaStreamSynchronize(h->s_main));
   release(d_seq);
   if (rc) return rc;
   u32 err = 0;
   CK(cudaMemcpy(&err, (char *)h->d_misc.p + 8, 4, cudaMemcpyDeviceToHost));
-  if (err) return fail(h, KC_ERR_BADCHAR, "contig character outside ACGTN");
-  h->has_ctg = true;
-  h->st.num_seqs += n_ctgs;
+  if (err) return fail(h, KC_ERR_BADCHAR, "sequence character outside ACGTN");
+  if (is_ctg) h->has_ctg = true;
+  h->st.num_seqs += n_seqs;
   h->st.num_bases += b1 - b0;
+  return KC_OK;
+}
+
+}  // namespace
+
+extern "C" int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs) {
+  return add_ascii(h, seqs, offsets, depths, n_ctgs, true);
+}
+
+extern "C" int kc_add_reads_ascii(kc_handle *h, const char *seqs, const uint64_t *offsets, uint64_t n_reads) {
+  return add_ascii(h, seqs, offsets, nullptr, n_reads, false);
+}
+
+extern "C" int kc_set_dmin_thres(kc_handle *h, int32_t dmin_thres) {
+  if (!h) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "already finished");
+  if (dmin_thres < 1) return fail(h, KC_ERR_INVALID, "dmin_thres must be >= 1");
+  h->cfg.dmin_thres = dmin_thres;
   return KC_OK;
 }
 
@@ -702,8 +800,8 @@ int finish_count(kc_handle *h) {
   CK(cudaMemcpy(&inst_parsed, h->d_misc.p, 8, cudaMemcpyDeviceToHost));
   h->st.instances_parsed = inst_parsed;
   // supermer buffers are no longer needed (KmerDHT::clear_stores, kmer_dht.cpp:156-159)
-  for (auto &b : h->blocks) { cudaFree(b.hdr); cudaFree(b.payload); }
-  for (auto &b : h->rblocks) { cudaFree(b.hdr); cudaFree(b.payload); }
+  for (auto &b : h->blocks) { dev_free(b.hdr); dev_free(b.payload); }
+  for (auto &b : h->rblocks) { dev_free(b.hdr); dev_free(b.payload); }
   h->blocks.clear();
   h->rblocks.clear();
   h->finished = true;
@@ -769,13 +867,33 @@ extern "C" int kc_get_stats(kc_handle *h, kc_stats *st) {
   return KC_OK;
 }
 
+extern "C" int kc_release_cached_memory(void) {
+  DevCache &c = dev_cache();
+  std::vector<std::pair<int, void *>> drop;
+  {
+    std::lock_guard<std::mutex> lk(c.mu);
+    for (auto &d : c.free_blocks) {
+      for (auto &kv : d.second) drop.push_back({d.first, kv.second});
+      d.second.clear();
+    }
+  }
+  int cur = 0;
+  cudaGetDevice(&cur);
+  for (auto &x : drop) {
+    cudaSetDevice(x.first);
+    cudaFree(x.second);
+  }
+  cudaSetDevice(cur);
+  return KC_OK;
+}
+
 extern "C" int kc_destroy(kc_handle *h) {
   if (!h) return KC_OK;
   cudaSetDevice(h->cfg.device);
   if (h->s_main) cudaStreamSynchronize(h->s_main);
   if (h->s_copy) cudaStreamSynchronize(h->s_copy);
-  for (auto &b : h->blocks) { cudaFree(b.hdr); cudaFree(b.payload); }
-  for (auto &b : h->rblocks) { cudaFree(b.hdr); cudaFree(b.payload); }
+  for (auto &b : h->blocks) { dev_free(b.hdr); dev_free(b.payload); }
+  for (auto &b : h->rblocks) { dev_free(b.hdr); dev_free(b.payload); }
   DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_hist, &h->d_cursor,
                     &h->d_hdr_base, &h->d_pay_base, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
                     &h->pf_keys, &h->pf_vals};

@@ -203,7 +203,7 @@ int kc_exchange(kc_handle *h) {
   std::vector<BucketHist *> d_dirs(h->blocks.size(), nullptr);
   for (size_t b = 0; b < h->blocks.size(); b++) {
     if (!h->blocks[b].tot_sup) continue;
-    CK(cudaMalloc((void **)&d_dirs[b], sizeof(BucketHist) * (size_t)N * P));
+    CK(dev_alloc((void **)&d_dirs[b], sizeof(BucketHist) * (size_t)N * P));
     CK(cudaMemcpyAsync(d_dirs[b], h->blocks[b].hist.data(), sizeof(BucketHist) * (size_t)N * P, cudaMemcpyHostToDevice, st));
   }
   // 4. receive buffers
@@ -216,9 +216,9 @@ int kc_exchange(kc_handle *h) {
       const u64 nsup = r[1 + 2 * me], nwords = r[2 + 2 * me];
       if (!nsup) continue;
       Incoming in{nullptr, nullptr, nullptr, nsup, nwords, r[0] != 0, s};
-      CK(cudaMalloc((void **)&in.dir, sizeof(BucketHist) * P));
-      CK(cudaMalloc((void **)&in.hdr, sizeof(SupHdr) * (nsup + 1)));
-      CK(cudaMalloc((void **)&in.payload, sizeof(u32) * (nwords + 8)));
+      CK(dev_alloc((void **)&in.dir, sizeof(BucketHist) * P));
+      CK(dev_alloc((void **)&in.hdr, sizeof(SupHdr) * (nsup + 1)));
+      CK(dev_alloc((void **)&in.payload, sizeof(u32) * (nwords + 8)));
       CK(cudaMemsetAsync(in.payload + nwords, 0, sizeof(u32) * 8, st));
       inc.push_back(in);
     }
@@ -252,10 +252,10 @@ int kc_exchange(kc_handle *h) {
   CK(cudaStreamSynchronize(st));
   for (size_t i = 0; i < inc.size(); i++) {
     make_rblock(h, &dirs[i * P], inc[i].hdr, inc[i].payload, inc[i].ctg);
-    cudaFree(inc[i].dir);
+    dev_free(inc[i].dir);
   }
   for (auto p : d_dirs)
-    if (p) cudaFree(p);
+    if (p) dev_free(p);
   release(d_meta);
   release(d_all);
   h->st.ms_exchange += elapsed(e0, e1);
@@ -295,8 +295,8 @@ extern "C" int kc_finish_local_group(kc_handle **hs, int32_t n) {
         SupHdr *hdr = nullptr;
         u32 *pay = nullptr;
         CK(cudaSetDevice(hd->cfg.device));
-        CK(cudaMalloc((void **)&hdr, sizeof(SupHdr) * (nsup + 1)));
-        CK(cudaMalloc((void **)&pay, sizeof(u32) * (nwords + 8)));
+        CK(dev_alloc((void **)&hdr, sizeof(SupHdr) * (nsup + 1)));
+        CK(dev_alloc((void **)&pay, sizeof(u32) * (nwords + 8)));
         CK(cudaMemset(pay + nwords, 0, sizeof(u32) * 8));
         CK(cudaMemcpyPeer(hdr, hd->cfg.device, blk.hdr + blk.hdr_base[(size_t)d * P], h->cfg.device, sizeof(SupHdr) * nsup));
         CK(cudaMemcpyPeer(pay, hd->cfg.device, blk.payload + blk.pay_base[(size_t)d * P], h->cfg.device, sizeof(u32) * nwords));

@@ -36,7 +36,7 @@ class KcStats(C.Structure):
 
 
 EXPORTS = [
-    "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_add_reads", "kc_add_reads_device", "kc_add_contigs",
+    "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
     "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
 ]
@@ -63,6 +63,8 @@ def load_library():
     lib.kc_add_reads.argtypes = [vp, vp, vp, u64]
     lib.kc_add_reads_device.argtypes = [vp, vp, vp, u64, u64, C.c_uint32]
     lib.kc_add_contigs.argtypes = [vp, vp, vp, vp, u64]
+    lib.kc_add_reads_ascii.argtypes = [vp, vp, vp, u64]
+    lib.kc_set_dmin_thres.argtypes = [vp, i32]
     lib.kc_comm_unique_id.argtypes = [vp]
     lib.kc_comm_init.argtypes = [vp, vp]
     lib.kc_finish.argtypes = [vp]
@@ -136,6 +138,15 @@ class KmerCounter:
         co = np.ascontiguousarray(offsets, dtype=np.uint64)
         cd = np.ascontiguousarray(depths, dtype=np.float64)
         self._ck(self.lib.kc_add_contigs(self.h, _ptr(cs), _ptr(co), _ptr(cd), len(co) - 1), "kc_add_contigs")
+
+    def add_reads_ascii(self, seqs, offsets):
+        """Reads as ASCII ACGTN, lower case = low quality (the form SeqBlockInserter::process_seq receives)."""
+        cs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        co = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self._ck(self.lib.kc_add_reads_ascii(self.h, _ptr(cs), _ptr(co), len(co) - 1), "kc_add_reads_ascii")
+
+    def set_dmin_thres(self, v):
+        self._ck(self.lib.kc_set_dmin_thres(self.h, v), "kc_set_dmin_thres")
 
     def comm_init(self, unique_id_bytes):
         buf = (C.c_uint8 * 128).from_buffer_copy(bytes(unique_id_bytes))

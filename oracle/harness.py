@@ -249,3 +249,48 @@ if __name__ == "__main__":
     import sys
     if len(sys.argv) > 1 and sys.argv[1] == "phase":
         _phase_main(sys.argv[2:])
+
+
+# ---- drop-in proof: the reference's own analyze_kmers with integration/kcount_b200.cpp as its backend (dropin_driver.cpp) ----
+DROPIN_SO = os.path.join(HERE, "_ref", "libkcount_dropin.so")
+
+
+def have_dropin():
+    return os.path.exists(DROPIN_SO)
+
+
+def run_dropin(k, read_bytes, read_offsets, dmin_thres=2, qual_offset=33, ctg_seqs=None, ctg_offsets=None, ctg_depths=None):
+    """analyze_kmers<MAX_K> of the reference (kcount.cpp) over PackedReads + Contigs, kcount_b200.cpp behind it; returns the
+    contents of kmer_dht->local_kmers sorted by key. Needs a GPU (the binding drives libkcount_b200.so)."""
+    lib = C.CDLL(DROPIN_SO)
+    lib.odrop_run.restype = C.c_void_p
+    lib.odrop_run.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.odrop_n_longs.argtypes = [C.c_void_p]
+    lib.odrop_num_survivors.argtypes = [C.c_void_p]
+    lib.odrop_num_survivors.restype = C.c_uint64
+    lib.odrop_copy_survivors.argtypes = [C.c_void_p] * 5
+    lib.odrop_free.argtypes = [C.c_void_p]
+    rb = np.ascontiguousarray(read_bytes, dtype=np.uint8)
+    ro = np.ascontiguousarray(read_offsets, dtype=np.uint64)
+    cs = co = cd = None
+    n_ctgs = 0
+    if ctg_offsets is not None and len(ctg_offsets) > 1:
+        cs = np.ascontiguousarray(ctg_seqs, dtype=np.uint8)
+        co = np.ascontiguousarray(ctg_offsets, dtype=np.uint64)
+        cd = np.ascontiguousarray(ctg_depths, dtype=np.float64)
+        n_ctgs = len(co) - 1
+    h = lib.odrop_run(k, qual_offset, dmin_thres, _p(rb), _p(ro), len(ro) - 1, _p(cs), _p(co), _p(cd), n_ctgs)
+    if not h:
+        raise RuntimeError("drop-in run failed")
+    try:
+        res = OracleResult()
+        nl = res.n_longs = lib.odrop_n_longs(h)
+        n = lib.odrop_num_survivors(h)
+        res.keys = np.zeros((n, nl), dtype=np.uint64)
+        res.counts = np.zeros(n, dtype=np.uint16)
+        res.left = np.zeros(n, dtype=np.uint8)
+        res.right = np.zeros(n, dtype=np.uint8)
+        lib.odrop_copy_survivors(h, _p(res.keys), _p(res.counts), _p(res.left), _p(res.right))
+        return res
+    finally:
+        lib.odrop_free(h)

@@ -43,9 +43,20 @@ def test_no_gpu_means_loud_failure(built):
         kcount.KmerCounter(31)
 
 
+def test_dropin_binding_builds_against_reference_headers(built):
+    """integration/kcount_b200.cpp (the reference-side binding) compiles together with the reference's unmodified kcount.cpp,
+    kmer_dht.cpp and kmer.cpp, and the result links against libkcount_b200.so (built only where /root/reference exists)."""
+    from oracle import harness
+    if not harness.have_dropin():
+        pytest.skip("drop-in build not present (no /root/reference)")
+    lib = ctypes.CDLL(harness.DROPIN_SO)
+    for name in ("odrop_run", "odrop_num_survivors", "odrop_copy_survivors", "odrop_free"):
+        assert hasattr(lib, name)
+
+
 def test_product_never_imports_oracle():
-    pkg = os.path.join(ROOT, "mhm2_proxy_b200")
-    for dirpath, _, files in os.walk(pkg):
+    for pkg in (os.path.join(ROOT, "mhm2_proxy_b200"), os.path.join(ROOT, "integration")):
+      for dirpath, _, files in os.walk(pkg):
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h", ".inl")):
                 src = open(os.path.join(dirpath, f)).read()

@@ -218,6 +218,39 @@ def test_against_reference_build(built, community, k):
     _assert_same(gpu, ref, f"reference build k={k}")
 
 
+@pytest.mark.skipif(not __import__("oracle.harness", fromlist=["x"]).have_dropin(), reason="drop-in build not present")
+@pytest.mark.parametrize("k,thres", [(21, 2), (33, 3), (55, 2), (99, 2)])
+def test_dropin_through_reference_analyze_kmers(built, community, k, thres):
+    """The drop-in boundary itself: the reference's OWN analyze_kmers<MAX_K> (kcount.cpp, compiled unmodified) driving
+    integration/kcount_b200.cpp (SeqBlockInserter / HashTableInserter over the C ABI) must leave in kmer_dht->local_kmers
+    exactly what the reference's CPU backend leaves there."""
+    from oracle import harness
+    rb, ro = synth.make_reads(5000, community, error_rate=0.01, seed=700 + k, n_rate=1e-3)
+    cs, co, cd = synth.make_contigs(community, k, 40, seed=k + 11, depth_max=6)
+    got = harness.run_dropin(k, rb, ro, dmin_thres=thres, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd)
+    ref = _oracle(k, rb, ro, dmin_thres=thres, ctg_seqs=cs, ctg_offsets=co, ctg_depths=cd, prefer_ref=True)
+    _assert_same((got.keys, got.counts, got.left, got.right), ref, f"drop-in k={k}")
+    # reads only (no contig pass at all: fut_has_contigs is false, kcount.cpp:149)
+    got = harness.run_dropin(k, rb, ro, dmin_thres=thres)
+    _assert_same((got.keys, got.counts, got.left, got.right), _oracle(k, rb, ro, dmin_thres=thres), f"drop-in reads only k={k}")
+
+
+def test_reads_ascii_equals_packed(built, community):
+    """kc_add_reads_ascii (what process_seq receives: ASCII, lower case = low quality) == kc_add_reads (PackedRead bytes)."""
+    from mhm2_proxy_b200 import kcount
+    k = 31
+    rb, ro = synth.make_reads(4000, community, error_rate=0.01, seed=9, n_rate=2e-3, var_len=True)
+    lut = np.frombuffer(b"ACGTNNNN", dtype=np.uint8)
+    asc = lut[rb & 7]
+    asc = np.where((rb >> 3) < 20, asc | 0x20, asc).astype(np.uint8)
+    with kcount.KmerCounter(k, num_partitions=4) as kc:
+        kc.add_reads_ascii(asc, ro)
+        kc.set_dmin_thres(2)
+        kc.finish()
+        got = kc.survivors()
+    _assert_same(got, _oracle(k, rb, ro), "ascii reads")
+
+
 @pytest.mark.parametrize("n_shards,k", [(2, 21), (3, 33), (8, 31), (4, 99)])
 def test_sharded_table_matches_oracle_shards(built, community, n_shards, k):
     """N shards in one process on one GPU (local transport): reads split across shards, supermers routed to the owner
