@@ -32,11 +32,10 @@ struct DevBuf {
 
 // one parsed batch (or one received batch): supermers of every bucket laid out bucket-major
 struct Block {
-  SupHdr *hdr = nullptr;
-  u32 *payload = nullptr;
+  u32 *rec = nullptr;            // supermer records, rw words each, bucket-major
   std::vector<BucketHist> hist;  // per bucket of the PRODUCER (num_shards*P) for local blocks; P entries for received
-  std::vector<u64> hdr_base, pay_base;
-  u64 tot_sup = 0, tot_words = 0;
+  std::vector<u64> rec_base;     // index of each bucket's first record (+ total at the end)
+  u64 tot_sup = 0;
   bool is_ctg = false;
   bool received = false;  // true: indexed by partition only
 };
@@ -49,15 +48,15 @@ struct kc_handle {
   kc_config cfg;
   int KW = 1, m = 15, w = 1;
   int smem_optin = 0, sms = 0;
+  RecGeom geom;  // supermer record geometry for this k
   u32 P = 0;  // partitions per shard (0 until the first add decides)
   bool finished = false, has_ctg = false;
   cudaStream_t s_main = nullptr, s_copy = nullptr;
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
   std::vector<Block> blocks;       // produced locally
   std::vector<Block> rblocks;      // received from peers (multi-shard)
-  std::vector<BucketBase> h_base;  // staging for the per-batch bucket layout
   DevBuf stage_bytes[2], stage_offs[2];
-  DevBuf d_hist, d_cursor, d_hdr_base, d_pay_base, d_misc;  // d_misc: u64 instances, u32 err
+  DevBuf d_hist, d_cursor, d_base, d_misc;  // d_misc: u64 instances, u32 err
   // outputs
   DevBuf out_keys, out_counts, out_left, out_right, pf_keys, pf_vals;
   u64 n_surv = 0, n_pf = 0;
@@ -220,6 +219,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   if (m > k) m = k;  // reference asserts m <= k (kmer.cpp:346); only reachable for k < 15
   h->m = m;
   h->w = k - m + 1;
+  h->geom = rec_geom(k, h->w);
   int ndev = 0;
   CK(cudaGetDeviceCount(&ndev));
   if (cfg->device < 0 || cfg->device >= ndev) return fail(h, KC_ERR_INVALID, "device %d of %d", cfg->device, ndev);
@@ -247,14 +247,15 @@ namespace {
 void table_geometry(const kc_handle *h, bool wide, bool ctg, u32 &tab_size, u32 &key_cap) {
   const int KW = h->KW, VW = (wide ? VR_WIDE : VR_NARROW) + (ctg ? V_CTG : 0);
   const size_t budget = (size_t)h->smem_optin - 2048;  // static shared memory + alignment slack
-  const size_t fixed = count_smem_bytes(KW, VW, 0, 0, ctg) + 8;
+  const size_t fixed = count_smem_bytes(KW, VW, 0, 0) + 32;
   const size_t per_key = (size_t)KW * 8 + (size_t)VW * 4 + 8;  // + two 4-byte index-table entries (load <= 0.5)
   u64 cap = budget > fixed ? (budget - fixed) / per_key : 16;
   cap = std::min<u64>(cap, IDX_MASK - 1);
+  (void)ctg;
   if (h->cfg.dbg_key_cap > 0) cap = std::min<u64>(cap, (u64)h->cfg.dbg_key_cap);
   cap = std::max<u64>(cap, 16);
   key_cap = (u32)cap;
-  tab_size = (u32)((2 * cap + 3) & ~3ull);
+  tab_size = (u32)((2 * cap + 15) & ~15ull);  // whole 16-byte buckets; keeps what follows 16-byte aligned
 }
 
 void decide_partitions(kc_handle *h, u64 inst_estimate) {
@@ -286,7 +287,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   const u32 NP = h->P * (u32)h->cfg.num_shards;
   RC(ensure(h, h->d_hist, sizeof(BucketHist) * NP));
   RC(ensure(h, h->d_cursor, sizeof(BucketHist) * NP));
-  RC(ensure(h, h->d_hdr_base, sizeof(BucketBase) * NP));
+  RC(ensure(h, h->d_base, sizeof(u64) * NP));
   ParseArgs a;
   memset(&a, 0, sizeof(a));
   a.bytes = d_bytes;
@@ -307,16 +308,21 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   const int n16 = (15 + std::max(max_len, 16) + 15) >> 4;  // 16-byte chunks of the longest sequence at the worst alignment
   a.nsb = n16 + 4;
   a.nsv = (n16 + 1) / 2 + 2;
+  a.nwb = h->geom.nwb;
+  a.nwv = h->geom.nwv;
+  a.rw = h->geom.rw;
   a.instances = (u64 *)h->d_misc.p;
   a.err = (u32 *)((char *)h->d_misc.p + 8);
   const int words_per_thread = a.nsb + a.nsv + 2 * a.w + PARSE_LCAP / 2;
-  int threads = PARSE_THREADS;
+  int threads = 128;
   while (threads > 32 && (size_t)threads * words_per_thread * 4 > 96u * 1024u) threads >>= 1;
   const size_t smem = (size_t)threads * words_per_thread * 4;
-  CK(cudaFuncSetAttribute(parse_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  CK(cudaFuncSetAttribute(parse_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  void (*k_count)(const ParseArgs) = threads == 128 ? parse_kernel<false, 128> : threads == 64 ? parse_kernel<false, 64> : parse_kernel<false, 32>;
+  void (*k_fill)(const ParseArgs) = threads == 128 ? parse_kernel<true, 128> : threads == 64 ? parse_kernel<true, 64> : parse_kernel<true, 32>;
+  CK(cudaFuncSetAttribute(k_count, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  CK(cudaFuncSetAttribute(k_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, parse_kernel<true>, threads, smem));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fill, threads, smem));
   per_sm = std::max(per_sm, 1);
   const u64 need_blocks = (nseq + threads - 1) / threads;
   const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * per_sm * 2);
@@ -326,7 +332,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   // COUNT
   CK(cudaMemsetAsync(h->d_hist.p, 0, sizeof(BucketHist) * NP, h->s_main));
   a.hist = (BucketHist *)h->d_hist.p;
-  parse_kernel<false><<<grid, threads, smem, h->s_main>>>(a);
+  k_count<<<grid, threads, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
@@ -336,47 +342,38 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   blk.hist.resize(NP);
   CK(cudaMemcpyAsync(blk.hist.data(), h->d_hist.p, sizeof(BucketHist) * NP, cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
-  blk.hdr_base.resize(NP + 1);
-  blk.pay_base.resize(NP + 1);
-  u64 hs = 0, ps = 0;
+  blk.rec_base.resize(NP + 1);
+  u64 hs = 0;
   for (u32 b = 0; b < NP; b++) {
-    blk.hdr_base[b] = hs;
-    blk.pay_base[b] = ps;
+    blk.rec_base[b] = hs;
     hs += blk.hist[b].nsup;
-    ps += blk.hist[b].nwords;
   }
-  blk.hdr_base[NP] = hs;
-  blk.pay_base[NP] = ps;
+  blk.rec_base[NP] = hs;
   blk.tot_sup = hs;
-  blk.tot_words = ps;
   if (hs == 0) {
     CK(cudaEventRecord(e1, h->s_main));
     return KC_OK;
   }
-  CK(dev_alloc((void **)&blk.hdr, sizeof(SupHdr) * (hs + 1)));
-  CK(dev_alloc((void **)&blk.payload, sizeof(u32) * (ps + 8)));  // + slack: fetch64 may read 2 words past a record
-  CK(cudaMemsetAsync(blk.payload + ps, 0, sizeof(u32) * 8, h->s_main));
-  h->h_base.resize(NP);
-  for (u32 b = 0; b < NP; b++) h->h_base[b] = BucketBase{blk.hdr_base[b], blk.pay_base[b]};
-  CK(cudaMemcpyAsync(h->d_hdr_base.p, h->h_base.data(), sizeof(BucketBase) * NP, cudaMemcpyHostToDevice, h->s_main));
+  const size_t rec_bytes = (size_t)hs * a.rw * 4;
+  CK(dev_alloc((void **)&blk.rec, rec_bytes + 64));
+  CK(cudaMemcpyAsync(h->d_base.p, blk.rec_base.data(), sizeof(u64) * NP, cudaMemcpyHostToDevice, h->s_main));
   CK(cudaMemsetAsync(h->d_cursor.p, 0, sizeof(BucketHist) * NP, h->s_main));
   // FILL
   a.hist = (BucketHist *)h->d_cursor.p;
-  a.base = (const BucketBase *)h->d_hdr_base.p;
-  a.hdr = blk.hdr;
-  a.payload = blk.payload;
+  a.base = (const u64 *)h->d_base.p;
+  a.rec = blk.rec;
   CK(cudaEventRecord(h->ev_d, h->s_main));
-  parse_kernel<true><<<grid, threads, smem, h->s_main>>>(a);
+  k_fill<<<grid, threads, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
   CK(cudaEventRecord(e1, h->s_main));
-  CK(cudaStreamSynchronize(h->s_main));  // hdr_base/pay_base host vectors are about to move; also surfaces kernel faults here
+  CK(cudaStreamSynchronize(h->s_main));  // rec_base is about to move; also surfaces kernel faults here
   h->st.ms_parse += elapsed(e0, e1);
   h->st.ms_parse_count += elapsed(e0, h->ev_c);
   h->st.ms_parse_fill += elapsed(h->ev_d, e1);
   h->st.supermers_out += hs;
-  h->st.supermer_bytes_out += hs * sizeof(SupHdr) + ps * 4;
+  h->st.supermer_bytes_out += rec_bytes;
   h->blocks.push_back(std::move(blk));
   return KC_OK;
 }
@@ -659,8 +656,7 @@ int finish_count(kc_handle *h) {
       const u32 bu = first_bucket[bi] + p;
       if (!b.hist[bu].nsup) continue;
       SegDesc sd;
-      sd.hdr = b.hdr + b.hdr_base[bu];
-      sd.payload = b.payload + b.pay_base[bu];
+      sd.rec = b.rec + (size_t)b.rec_base[bu] * h->geom.rw;
       sd.nsup = b.hist[bu].nsup;
       sd.is_ctg = b.is_ctg ? 1 : 0;
       sd.sup0 = (u32)nsup;
@@ -705,6 +701,8 @@ int finish_count(kc_handle *h) {
   memset(&ca, 0, sizeof(ca));
   ca.segs = (const SegDesc *)d_segs.p;
   ca.k = h->cfg.kmer_len;
+  ca.rw = h->geom.rw;
+  ca.nwb = h->geom.nwb;
   ca.dmin_thres = h->cfg.dmin_thres;
   ca.frac = 1.0 - h->cfg.dyn_min_depth;  // kcount_cpu.cpp:178, evaluated in fp64 exactly as the reference does
   ca.out_keys = (u64 *)h->out_keys.p;
@@ -735,7 +733,7 @@ int finish_count(kc_handle *h) {
     u32 tab_size, key_cap;
     table_geometry(h, wide, any_ctg, tab_size, key_cap);
     const int VW = (wide ? VR_WIDE : VR_NARROW) + (any_ctg ? V_CTG : 0);
-    const size_t smem = count_smem_bytes(KW, VW, tab_size, key_cap, any_ctg) + 8;
+    const size_t smem = count_smem_bytes(KW, VW, tab_size, key_cap) + 8;
     RC(ensure(h, d_items, items.size() * sizeof(WorkItem)));
     RC(ensure(h, d_status, items.size() * sizeof(ItemStatus)));
     CK(cudaMemcpyAsync(d_items.p, items.data(), items.size() * sizeof(WorkItem), cudaMemcpyHostToDevice, h->s_main));
@@ -800,8 +798,8 @@ int finish_count(kc_handle *h) {
   CK(cudaMemcpy(&inst_parsed, h->d_misc.p, 8, cudaMemcpyDeviceToHost));
   h->st.instances_parsed = inst_parsed;
   // supermer buffers are no longer needed (KmerDHT::clear_stores, kmer_dht.cpp:156-159)
-  for (auto &b : h->blocks) { dev_free(b.hdr); dev_free(b.payload); }
-  for (auto &b : h->rblocks) { dev_free(b.hdr); dev_free(b.payload); }
+  for (auto &b : h->blocks) dev_free(b.rec);
+  for (auto &b : h->rblocks) dev_free(b.rec);
   h->blocks.clear();
   h->rblocks.clear();
   h->finished = true;
@@ -892,10 +890,10 @@ extern "C" int kc_destroy(kc_handle *h) {
   cudaSetDevice(h->cfg.device);
   if (h->s_main) cudaStreamSynchronize(h->s_main);
   if (h->s_copy) cudaStreamSynchronize(h->s_copy);
-  for (auto &b : h->blocks) { dev_free(b.hdr); dev_free(b.payload); }
-  for (auto &b : h->rblocks) { dev_free(b.hdr); dev_free(b.payload); }
+  for (auto &b : h->blocks) dev_free(b.rec);
+  for (auto &b : h->rblocks) dev_free(b.rec);
   DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_hist, &h->d_cursor,
-                    &h->d_hdr_base, &h->d_pay_base, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
+                    &h->d_base, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
                     &h->pf_keys, &h->pf_vals};
   for (DevBuf *b : bufs) release(*b);
   if (h->ev_a) cudaEventDestroy(h->ev_a);

@@ -21,27 +21,21 @@
 namespace {
 
 // a received run: directory (P entries) already on the host, hdr/payload device buffers owned by the block
-int make_rblock(kc_handle *h, const BucketHist *dir, SupHdr *hdr, u32 *payload, bool is_ctg) {
+int make_rblock(kc_handle *h, const BucketHist *dir, u32 *rec, bool is_ctg) {
   const u32 P = h->P;
   Block b;
   b.received = true;
   b.is_ctg = is_ctg;
-  b.hdr = hdr;
-  b.payload = payload;
+  b.rec = rec;
   b.hist.assign(dir, dir + P);
-  b.hdr_base.resize(P + 1);
-  b.pay_base.resize(P + 1);
-  u64 hs = 0, ps = 0;
+  b.rec_base.resize(P + 1);
+  u64 hs = 0;
   for (u32 p = 0; p < P; p++) {
-    b.hdr_base[p] = hs;
-    b.pay_base[p] = ps;
+    b.rec_base[p] = hs;
     hs += dir[p].nsup;
-    ps += dir[p].nwords;
   }
-  b.hdr_base[P] = hs;
-  b.pay_base[P] = ps;
+  b.rec_base[P] = hs;
   b.tot_sup = hs;
-  b.tot_words = ps;
   h->rblocks.push_back(std::move(b));
   return KC_OK;
 }
@@ -182,15 +176,15 @@ int kc_exchange(kc_handle *h) {
     maxb = std::max(maxb, all[2 * r + 1]);
   }
   if (maxb == 0) return KC_OK;
-  // 2. ... then on every (block, destination) size: per block [is_ctg, (nsup, nwords) x N]
-  const size_t rec = 1 + 2 * (size_t)N, per_rank = maxb * rec;
+  // 2. ... then on every (block, destination) size: per block [is_ctg, nsup x N]
+  const size_t rec = 1 + (size_t)N, per_rank = maxb * rec;
+  const size_t RB = (size_t)h->geom.rw * 4;  // bytes per supermer record
   std::vector<u64> sz(per_rank, 0), szall(per_rank * N);
   for (size_t b = 0; b < h->blocks.size(); b++) {
     const Block &blk = h->blocks[b];
     sz[b * rec] = blk.is_ctg ? 1 : 0;
     for (int d = 0; d < N; d++) {
-      sz[b * rec + 1 + 2 * d] = blk.tot_sup ? blk.hdr_base[(size_t)(d + 1) * P] - blk.hdr_base[(size_t)d * P] : 0;
-      sz[b * rec + 2 + 2 * d] = blk.tot_sup ? blk.pay_base[(size_t)(d + 1) * P] - blk.pay_base[(size_t)d * P] : 0;
+      sz[b * rec + 1 + d] = blk.tot_sup ? blk.rec_base[(size_t)(d + 1) * P] - blk.rec_base[(size_t)d * P] : 0;
     }
   }
   RC(ensure(h, d_meta, per_rank * 8));
@@ -207,19 +201,17 @@ int kc_exchange(kc_handle *h) {
     CK(cudaMemcpyAsync(d_dirs[b], h->blocks[b].hist.data(), sizeof(BucketHist) * (size_t)N * P, cudaMemcpyHostToDevice, st));
   }
   // 4. receive buffers
-  struct Incoming { BucketHist *dir; SupHdr *hdr; u32 *payload; u64 nsup, nwords; bool ctg; int src; };
+  struct Incoming { BucketHist *dir; u32 *rec; u64 nsup; bool ctg; int src; };
   std::vector<Incoming> inc;
   for (int s = 0; s < N; s++) {
     if (s == me) continue;
     for (u64 b = 0; b < all[2 * s + 1]; b++) {
       const u64 *r = &szall[(size_t)s * per_rank + b * rec];
-      const u64 nsup = r[1 + 2 * me], nwords = r[2 + 2 * me];
+      const u64 nsup = r[1 + me];
       if (!nsup) continue;
-      Incoming in{nullptr, nullptr, nullptr, nsup, nwords, r[0] != 0, s};
+      Incoming in{nullptr, nullptr, nsup, r[0] != 0, s};
       CK(dev_alloc((void **)&in.dir, sizeof(BucketHist) * P));
-      CK(dev_alloc((void **)&in.hdr, sizeof(SupHdr) * (nsup + 1)));
-      CK(dev_alloc((void **)&in.payload, sizeof(u32) * (nwords + 8)));
-      CK(cudaMemsetAsync(in.payload + nwords, 0, sizeof(u32) * 8, st));
+      CK(dev_alloc((void **)&in.rec, RB * nsup + 64));
       inc.push_back(in);
     }
   }
@@ -230,18 +222,16 @@ int kc_exchange(kc_handle *h) {
     if (d == me) continue;
     for (size_t b = 0; b < h->blocks.size(); b++) {
       const Block &blk = h->blocks[b];
-      const u64 nsup = sz[b * rec + 1 + 2 * d], nwords = sz[b * rec + 2 + 2 * d];
+      const u64 nsup = sz[b * rec + 1 + d];
       if (!nsup) continue;
       NC(a.Send(d_dirs[b] + (size_t)d * P, sizeof(BucketHist) * P, ncclUint8, d, h->comm->comm, st));
-      NC(a.Send(blk.hdr + blk.hdr_base[(size_t)d * P], sizeof(SupHdr) * nsup, ncclUint8, d, h->comm->comm, st));
-      NC(a.Send(blk.payload + blk.pay_base[(size_t)d * P], sizeof(u32) * nwords, ncclUint8, d, h->comm->comm, st));
-      sent += sizeof(BucketHist) * P + sizeof(SupHdr) * nsup + sizeof(u32) * nwords;
+      NC(a.Send(blk.rec + blk.rec_base[(size_t)d * P] * h->geom.rw, RB * nsup, ncclUint8, d, h->comm->comm, st));
+      sent += sizeof(BucketHist) * P + RB * nsup;
     }
   }
   for (auto &in : inc) {
     NC(a.Recv(in.dir, sizeof(BucketHist) * P, ncclUint8, in.src, h->comm->comm, st));
-    NC(a.Recv(in.hdr, sizeof(SupHdr) * in.nsup, ncclUint8, in.src, h->comm->comm, st));
-    NC(a.Recv(in.payload, sizeof(u32) * in.nwords, ncclUint8, in.src, h->comm->comm, st));
+    NC(a.Recv(in.rec, RB * in.nsup, ncclUint8, in.src, h->comm->comm, st));
   }
   NC(a.GroupEnd());
   // 6. directories back to the host -> rblocks
@@ -251,7 +241,7 @@ int kc_exchange(kc_handle *h) {
   CK(cudaEventRecord(e1, st));
   CK(cudaStreamSynchronize(st));
   for (size_t i = 0; i < inc.size(); i++) {
-    make_rblock(h, &dirs[i * P], inc[i].hdr, inc[i].payload, inc[i].ctg);
+    make_rblock(h, &dirs[i * P], inc[i].rec, inc[i].ctg);
     dev_free(inc[i].dir);
   }
   for (auto p : d_dirs)
@@ -288,20 +278,16 @@ extern "C" int kc_finish_local_group(kc_handle **hs, int32_t n) {
       if (!blk.tot_sup) continue;
       for (int d = 0; d < n; d++) {
         if (d == s) continue;
-        const u64 nsup = blk.hdr_base[(size_t)(d + 1) * P] - blk.hdr_base[(size_t)d * P];
-        const u64 nwords = blk.pay_base[(size_t)(d + 1) * P] - blk.pay_base[(size_t)d * P];
+        const u64 nsup = blk.rec_base[(size_t)(d + 1) * P] - blk.rec_base[(size_t)d * P];
         if (!nsup) continue;
         kc_handle *hd = hs[d];
-        SupHdr *hdr = nullptr;
-        u32 *pay = nullptr;
+        const size_t RB = (size_t)h->geom.rw * 4;
+        u32 *rec = nullptr;
         CK(cudaSetDevice(hd->cfg.device));
-        CK(dev_alloc((void **)&hdr, sizeof(SupHdr) * (nsup + 1)));
-        CK(dev_alloc((void **)&pay, sizeof(u32) * (nwords + 8)));
-        CK(cudaMemset(pay + nwords, 0, sizeof(u32) * 8));
-        CK(cudaMemcpyPeer(hdr, hd->cfg.device, blk.hdr + blk.hdr_base[(size_t)d * P], h->cfg.device, sizeof(SupHdr) * nsup));
-        CK(cudaMemcpyPeer(pay, hd->cfg.device, blk.payload + blk.pay_base[(size_t)d * P], h->cfg.device, sizeof(u32) * nwords));
-        make_rblock(hd, &blk.hist[(size_t)d * P], hdr, pay, blk.is_ctg);
-        h->st.supermer_bytes_sent += sizeof(SupHdr) * nsup + sizeof(u32) * nwords;
+        CK(dev_alloc((void **)&rec, RB * nsup + 64));
+        CK(cudaMemcpyPeer(rec, hd->cfg.device, blk.rec + blk.rec_base[(size_t)d * P] * h->geom.rw, h->cfg.device, RB * nsup));
+        make_rblock(hd, &blk.hist[(size_t)d * P], rec, blk.is_ctg);
+        h->st.supermer_bytes_sent += RB * nsup;
       }
     }
   }

@@ -1,17 +1,19 @@
 // Stage B — count: one CTA owns one partition of the shard's k-mer space at a time and keeps that partition's whole
 // hash table in SHARED MEMORY (measured on B200, tools/ubench_atomics.cu: shared atomics 2.8 T/s chip-wide vs 0.19 T/s for
 // L2-resident global RED, i.e. 15x). Per work item (partition, sub-pass):
-//   1. stream the partition's supermers (from every parsed / received batch) through a small staging buffer,
-//   2. expand them to k-mer instances, canonicalise, hash (MurmurHash3 = Kmer::hash), find-or-claim the key, bump the
-//      extension counters with shared-memory atomics
+//   1. four independent 256-thread pipelines (named barriers) each stream a quarter of the partition's supermer records
+//      through their own staging buffer — while one waits for HBM the others compute — and all insert into ONE table;
+//   2. records are expanded to k-mer instances, canonicalised, hashed (MurmurHash3 = Kmer::hash), found or claimed, and
+//      the extension counters bumped with shared-memory atomics
 //         replaces get_kmers_and_exts + KmerMapExts::insert + insert_supermer_from_read/_from_ctg
-//         (reference src/kcount/kcount_cpu.cpp:231-267,307-406),
-//   3. scan the dense key store: depth filter + extension choice + compaction of survivors straight to the output arrays
+//         (reference src/kcount/kcount_cpu.cpp:231-267,307-406);
+//   3. the dense key store is scanned: depth filter + extension choice + compaction of survivors straight to the output
 //         replaces HashTableInserter::insert_into_local_hashtable + ExtCounts::get_ext (kcount_cpu.cpp:173-182,490-528).
-// The table never touches HBM: HBM traffic of this stage = supermers read once + survivors written once.
+// The table never touches HBM: HBM traffic of this stage = supermer records read once + survivors written once.
 //
-// Table layout in shared memory ("index table + dense store"):
-//   tab[tab_size]  u32   open addressing, entry = fingerprint(19 bits) | (dense index + 1)(13 bits), 0 = empty
+// Table layout in shared memory ("bucketised index + dense store"):
+//   tab[nbuckets]  uint4  open addressing over 16-byte buckets of four entries; entry = fingerprint(19 bits) |
+//                         (dense index + 1)(13 bits), 0 = empty. One 128-bit load resolves almost every lookup.
 //   keys[key_cap]  KW x u64, in order of first arrival; last word all-ones = dead entry (lost a same-key race)
 //   vals[key_cap]  VW x u32 counters:
 //        narrow: 10 x u16 halves {left A,C,G,T,none, right A,C,G,T, spare}; a half that wraps flags the item `wide`
@@ -30,15 +32,16 @@ namespace kc {
 constexpr u64 KEY_EMPTY = 0xFFFFFFFFFFFFFFFFULL;  // last key word of a real k-mer is never all ones: it has >= 2 zero
                                                   // trailing bits because N_LONGS = k/32 + 1 (main.cpp:170)
 constexpr int CNT_THREADS = 1024;
-constexpr int EXP_CAP = 4096;      // k-mer instances per chunk
-constexpr int STAGE_WORDS = 3072;  // supermer payload words per chunk
-constexpr int SEG_CACHE = 64;      // segment descriptors cached per group
-constexpr u32 IDX_BITS = 13, IDX_MASK = (1u << IDX_BITS) - 1u;  // dense index + 1 fits 13 bits: key_cap <= 8191
+constexpr int CNT_GROUPS = 4;          // independent pipelines per CTA
+constexpr int GRP_THREADS = CNT_THREADS / CNT_GROUPS;
+constexpr int GRP_STAGE_WORDS = 1024;  // staged record words per pipeline and chunk
+constexpr int GRP_EXP = 1024;          // k-mer instances per pipeline and chunk
+constexpr int SEG_CACHE = 64;          // segment descriptors cached per round
+constexpr u32 IDX_BITS = 13, IDX_MASK = (1u << IDX_BITS) - 1u;  // dense index + 1 fits 13 bits: key_cap <= 8190
 constexpr int VR_NARROW = 5, VR_WIDE = 9, V_CTG = 3;
 
-struct SegDesc {  // one contiguous run of supermers of one partition inside one parsed / received batch
-  const SupHdr *hdr;
-  const u32 *payload;  // the run's payload region; SupHdr::woff is relative to it
+struct SegDesc {  // one contiguous run of supermer records of one partition inside one parsed / received batch
+  const u32 *rec;
   u32 nsup;
   u32 is_ctg;
   u32 sup0;  // index of the run's first supermer inside the partition's concatenation of runs
@@ -67,7 +70,8 @@ struct CountArgs {
   u32 nitems;
   u32 *next_item;  // dynamic scheduler
   int k;
-  u32 tab_size, key_cap;
+  int rw, nwb;     // record geometry (kc_parse.cuh)
+  u32 tab_size, key_cap;  // tab_size u32 entries (multiple of 4)
   int dmin_thres;
   double frac;     // 1.0 - DYN_MIN_DEPTH computed on the host in fp64
   u64 *out_keys;   // [out_cap * KW]
@@ -80,10 +84,31 @@ struct CountArgs {
   u64 pf_cap;
 };
 
-__host__ __device__ inline size_t count_smem_bytes(int KW, int VW, u32 tab_size, u32 key_cap, bool ctg) {
-  size_t b = (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4);
-  b += (size_t)EXP_CAP * 2 + (size_t)(STAGE_WORDS + 4) * 4 + (size_t)CNT_THREADS * 4 * (ctg ? 2 : 1) + (size_t)SEG_CACHE * sizeof(SegDesc);
+__host__ __device__ inline size_t count_smem_bytes(int KW, int VW, u32 tab_size, u32 key_cap) {
+  size_t b = (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4) + 8;
+  b += (size_t)SEG_CACHE * sizeof(SegDesc) + (size_t)CNT_GROUPS * ((GRP_STAGE_WORDS + 4) * 4 + GRP_EXP * 2);
   return b;
+}
+
+__device__ __forceinline__ void group_barrier(int g) {
+  asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(GRP_THREADS) : "memory");
+}
+// barrier of one pipeline that also ORs a predicate over its threads: the result is the same in every thread, which a
+// plain read of a flag that another pipeline may be setting concurrently is not
+__device__ __forceinline__ bool group_barrier_or(int g, bool pred) {
+  u32 r;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %3, 0;\n\tbar.red.or.pred p, %1, %2, q;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(r)
+      : "r"(g + 1), "r"(GRP_THREADS), "r"((u32)pred)
+      : "memory");
+  return r != 0;
+}
+__device__ __forceinline__ uint4 lds128_volatile(const void *p) {
+  uint4 v;
+  const u32 a = (u32)__cvta_generic_to_shared(p);
+  asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
 }
 
 template <int KW, bool WIDE, bool CTG>
@@ -91,24 +116,31 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  u32 *tab = (u32 *)smem_raw;                              // [tab_size], tab_size % 4 == 0
-  u64 *keys = (u64 *)(tab + a.tab_size);                   // [key_cap * KW]
+  u32 *tab = (u32 *)smem_raw;                              // [tab_size], 16-byte buckets
+  u32 *stage_all = tab + a.tab_size;                       // [GROUPS][GRP_STAGE_WORDS + 4], 16-byte aligned
+  uint16_t *expl_all = (uint16_t *)(stage_all + CNT_GROUPS * (GRP_STAGE_WORDS + 4));  // [GROUPS][GRP_EXP]
+  u64 *keys = (u64 *)(expl_all + CNT_GROUPS * GRP_EXP);    // [key_cap * KW]
   u32 *vals = (u32 *)(keys + (size_t)a.key_cap * KW);      // [key_cap * VW]
-  SegDesc *segc = (SegDesc *)(vals + (size_t)a.key_cap * VW + ((a.key_cap * VW) & 1));  // 8-byte aligned
-  u32 *stage = (u32 *)(segc + SEG_CACHE);                  // [STAGE_WORDS + 4]
-  u32 *meta = stage + STAGE_WORDS + 4;                     // [CNT_THREADS] staged word offset | nb << 16
-  u32 *meta2 = meta + CNT_THREADS;                         // [CNT_THREADS] (CTG only) depth | is_ctg << 16
-  uint16_t *expl = (uint16_t *)(meta + CNT_THREADS * (CTG ? 2 : 1));  // [EXP_CAP] supermer-in-chunk | (k-mer - 1) << 10
+  SegDesc *segc = (SegDesc *)(vals + (size_t)a.key_cap * VW + ((a.key_cap * VW) & 1));  // [SEG_CACHE], 8-byte aligned
   __shared__ u64 s_obase[2];
-  __shared__ u32 s_item, s_nkeys, s_over, s_wide, s_total, s_live;
-  __shared__ u32 warp_k[32], warp_w[32], warp_c[32], warp_p[32];
+  __shared__ u32 s_item, s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed;
+  __shared__ u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];
+  __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int k = a.k;
+  const int grp = tid / GRP_THREADS, gt = tid % GRP_THREADS, gw = gt >> 5;
+  u32 *stage = stage_all + grp * (GRP_STAGE_WORDS + 4);
+  uint16_t *expl = expl_all + grp * GRP_EXP;
+  const int k = a.k, rw = a.rw;
   const int nw = (k + 31) >> 5;
   const u64 last_mask = (k & 31) ? (~0ULL << (64 - 2 * (k & 31))) : ~0ULL;
+  const u32 nbuckets = a.tab_size >> 2;
+  const int sup_per_chunk = min(GRP_THREADS, GRP_STAGE_WORDS / rw);
   u32 my_max_probe = 0;
+  if (tid == 0) s_prev = a.key_cap;  // shared memory starts undefined: the first item clears every counter
 
   for (;;) {
+    __syncthreads();
+    const u32 prev = s_prev;
     __syncthreads();
     if (tid == 0) {
       s_item = atomicAdd(a.next_item, 1u);
@@ -116,76 +148,80 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       s_over = 0;
       s_wide = 0;
       s_live = 0;
+      s_consumed = 0;
     }
-    for (u32 i = tid; i < a.tab_size / 4; i += CNT_THREADS) ((uint4 *)tab)[i] = make_uint4(0, 0, 0, 0);
+    for (u32 i = tid; i < nbuckets; i += CNT_THREADS) ((uint4 *)tab)[i] = make_uint4(0, 0, 0, 0);
+    for (u32 i = tid; i < prev * VW; i += CNT_THREADS) vals[i] = 0;  // counters of the slots the previous item used
     __syncthreads();
     const u32 item_idx = s_item;
     if (item_idx >= a.nitems) break;
     const WorkItem it = a.items[item_idx];
     const u32 nseg = it.seg_end - it.seg_begin;
-    u32 consumed = 0;
-    bool over = false;
 
-    for (u32 sg0 = 0; sg0 < nseg && !over; sg0 += SEG_CACHE) {
+    for (u32 sg0 = 0; sg0 < nseg; sg0 += SEG_CACHE) {
       const int ns = (int)min((u32)SEG_CACHE, nseg - sg0);
       __syncthreads();
+      if (s_over) break;
       if (tid < ns) segc[tid] = a.segs[it.seg_begin + sg0 + tid];
       __syncthreads();
-      const u32 end_sup = segc[ns - 1].sup0 + segc[ns - 1].nsup;
-      u32 c0 = segc[0].sup0;
-      int seg_hint = 0;  // first segment that can contain c0
-      while (c0 < end_sup) {
-        // ---- a. one supermer header per thread ----
-        const u32 g = c0 + (u32)tid;
-        u32 nk = 0, nwd = 0, nb = 0, depth = 1, isc = 0;
-        const u32 *src = nullptr;
-        if (g < end_sup) {
+      const u32 r_lo = segc[0].sup0, r_hi = segc[ns - 1].sup0 + segc[ns - 1].nsup;
+      const u32 span = r_hi - r_lo;
+      const u32 g_lo = r_lo + (u32)(((u64)span * grp) / CNT_GROUPS), g_hi = r_lo + (u32)(((u64)span * (grp + 1)) / CNT_GROUPS);
+      u32 c0 = g_lo;
+      int seg_hint = 0;
+      while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
+      u32 consumed = 0;
+      while (c0 < g_hi) {
+        // ---- a. one supermer record per thread: copy it to the staging buffer ----
+        const u32 g = c0 + (u32)gt;
+        const bool have = gt < sup_per_chunk && g < g_hi;
+        u32 nk = 0;
+        if (have) {
           int si = seg_hint;
           while (si + 1 < ns && segc[si + 1].sup0 <= g) si++;
-          const SupHdr h = segc[si].hdr[g - segc[si].sup0];
-          nb = h.nb;
-          depth = h.depth;
-          isc = segc[si].is_ctg;
-          nk = nb - (u32)k - 1u;
-          nwd = ((nb + 15) >> 4) + ((nb + 31) >> 5);
-          src = segc[si].payload + h.woff;
+          const uint4 *src = (const uint4 *)(segc[si].rec + (size_t)(g - segc[si].sup0) * rw);
+          uint4 *dst = (uint4 *)(stage + gt * rw);
+          uint4 v = __ldg(src);
+          nk = (v.x & 0xFFFFu) - (u32)k - 1u;
+          if (CTG) v.x |= segc[si].is_ctg << 15;  // nb <= 256: bit 15 of the header is free
+          dst[0] = v;
+          for (int x = 1; x < (rw >> 2); x++) dst[x] = __ldg(src + x);
         }
-        // ---- b. block inclusive scans of k-mer and word counts; how many supermers fit this chunk ----
-        u32 ik = nk, iw = nwd;
+        // ---- b. scan of the k-mer counts inside the pipeline; how many supermers fit this chunk ----
+        u32 ik = nk;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-          const u32 yk = __shfl_up_sync(0xffffffffu, ik, d), yw = __shfl_up_sync(0xffffffffu, iw, d);
-          if (lane >= d) { ik += yk; iw += yw; }
+          const u32 y = __shfl_up_sync(0xffffffffu, ik, d);
+          if (lane >= d) ik += y;
         }
-        if (lane == 31) { warp_k[wid] = ik; warp_w[wid] = iw; }
-        __syncthreads();
-        u32 bk = 0, bw = 0;
-        for (int i = 0; i < wid; i++) { bk += warp_k[i]; bw += warp_w[i]; }
-        ik += bk;
-        iw += bw;
-        const bool fits = (g < end_sup) && ik <= (u32)EXP_CAP && iw <= (u32)STAGE_WORDS;
-        const u32 n_take = (u32)__syncthreads_count(fits);  // prefix sums are monotone: the fitting ones are a prefix
-        // ---- c. stage the payload, expand to instances ----
+        if (lane == 31) gw_k[grp][gw] = ik;
+        group_barrier(grp);
+        u32 pre = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) pre += (i < gw) ? gw_k[grp][i] : 0u;
+        ik += pre;
+        const bool fits = have && ik <= (u32)GRP_EXP;  // prefix sums are monotone: the fitting ones are a prefix
+        const u32 fm = __ballot_sync(0xffffffffu, fits);
+        const u32 fsum = __reduce_add_sync(0xffffffffu, fits ? nk : 0u);
+        if (lane == 0) { gw_c[grp][gw] = __popc(fm); gw_s[grp][gw] = fsum; }
         if (fits) {
-          const u32 woff = iw - nwd, koff = ik - nk;
-          meta[tid] = woff | (nb << 16);
-          if (CTG) meta2[tid] = depth | (isc << 16);
-          for (u32 x = 0; x < nwd; x++) stage[woff + x] = __ldg(src + x);
-          for (u32 j = 0; j < nk; j++) expl[koff + j] = (uint16_t)((u32)tid | (j << 10));
+          const u32 koff = ik - nk;
+          for (u32 j = 0; j < nk; j++) expl[koff + j] = (uint16_t)((u32)gt | (j << 8));
         }
-        if (tid == (int)n_take - 1) s_total = ik;  // total instances of the chunk
-        __syncthreads();
-        const u32 total = s_total;
+        group_barrier(grp);
+        u32 n_take = 0, total = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) { n_take += gw_c[grp][i]; total += gw_s[grp][i]; }
 
-        // ---- d. every k-mer instance of the chunk ----
-        for (u32 t = tid; t < total; t += CNT_THREADS) {
+        // ---- c. every k-mer instance of the chunk ----
+        for (u32 t = gt; t < total; t += GRP_THREADS) {
           const u32 e = expl[t];
-          const u32 si = e & 1023u;
-          const int j = (int)(e >> 10) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
-          const u32 mt = meta[si];
-          const u32 snb = mt >> 16;
-          const u32 *p = stage + (mt & 0xFFFFu);
-          const u32 *pv = p + ((snb + 15) >> 4);
+          const u32 si = e & 255u;
+          const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
+          const u32 *rec = stage + si * rw;
+          const u32 hdr = rec[0];
+          const u32 *p = rec + 1;
+          const u32 *pv = p + a.nwb;
           u64 fwd[KW], rc[KW];
 #pragma unroll
           for (int i = 0; i < KW; i++) fwd[i] = (i < nw) ? fetch64(p, j + 32 * i) : 0ULL;
@@ -211,55 +247,52 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           if (it.nsub > 1 && ((u32)(h >> 40) & (it.nsub - 1)) != it.sub) continue;
           // ---- find or claim ----
           const u32 fp = (u32)(h >> 32) & ~IDX_MASK;
-          u32 slot = __umulhi((u32)h, a.tab_size);
+          u32 bkt = __umulhi((u32)h, nbuckets);
           u32 mine = 0xFFFFFFFFu, idx = 0xFFFFFFFFu, probes = 0;
-          bool claimed = false;
+          bool claimed = false, full = false;
           for (;;) {
-            u32 en = ((volatile u32 *)tab)[slot];
-            if (en == 0) {
-              if (mine == 0xFFFFFFFFu) {  // reserve a dense entry (warp-aggregated), fill it, then publish it
-                const unsigned am = __activemask();
-                const int leader = __ffs(am) - 1;
-                u32 base = 0;
-                if (lane == leader) base = atomicAdd(&s_nkeys, (u32)__popc(am));
-                base = __shfl_sync(am, base, leader);
-                mine = base + (u32)__popc(am & ((1u << lane) - 1u));
-                if (mine >= a.key_cap) {
-                  s_over = 1;
+            const uint4 bq = lds128_volatile(tab + 4 * bkt);
+            u32 en4[4] = {bq.x, bq.y, bq.z, bq.w};
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              if (idx != 0xFFFFFFFFu || full) break;
+              u32 en = en4[q];
+              if (en == 0) {
+                if (mine == 0xFFFFFFFFu) {  // reserve a dense entry, fill it, then publish it
+                  mine = atomicAdd(&s_nkeys, 1u);
+                  if (mine >= a.key_cap) {
+                    s_over = 1;
+                    full = true;
+                    break;
+                  }
+#pragma unroll
+                  for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
+                  __threadfence_block();
+                }
+                en = atomicCAS(&tab[4 * bkt + q], 0u, fp | (mine + 1u));
+                if (en == 0) {
+                  idx = mine;
+                  claimed = true;
                   break;
                 }
-#pragma unroll
-                for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
-#pragma unroll
-                for (int i = 0; i < VW; i++) vals[(size_t)mine * VW + i] = 0u;
-                __threadfence_block();
               }
-              en = atomicCAS(&tab[slot], 0u, fp | (mine + 1u));
-              if (en == 0) {
-                idx = mine;
-                claimed = true;
-                break;
+              if ((en & ~IDX_MASK) == fp) {
+                const u32 cand = (en & IDX_MASK) - 1u;
+                bool same = true;
+#pragma unroll
+                for (int i = 0; i < KW; i++) same = same && (((volatile u64 *)keys)[(size_t)cand * KW + i] == key[i]);
+                if (same) idx = cand;
               }
             }
-            if ((en & ~IDX_MASK) == fp) {
-              const u32 cand = (en & IDX_MASK) - 1u;
-              bool same = true;
-#pragma unroll
-              for (int i = 0; i < KW; i++) same = same && (((volatile u64 *)keys)[(size_t)cand * KW + i] == key[i]);
-              if (same) {
-                idx = cand;
-                break;
-              }
-            }
+            if (idx != 0xFFFFFFFFu || full) break;
             probes++;
-            slot = (slot + 1 == a.tab_size) ? 0u : slot + 1;
+            bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
           }
           if (mine != 0xFFFFFFFFu && !claimed && mine < a.key_cap) keys[(size_t)mine * KW + KW - 1] = KEY_EMPTY;  // lost a same-key race
           if (idx == 0xFFFFFFFFu) continue;  // out of key slots; the item is re-run
           my_max_probe = max(my_max_probe, probes);
           u32 *v = vals + (size_t)idx * VW;
-          const u32 mt2 = CTG ? meta2[si] : 0u;
-          if (!CTG || !(mt2 >> 16)) {  // a read instance (count 1: kcount_cpu.cpp:75,348-352)
+          if (!CTG || !(hdr & 0x8000u)) {  // a read instance (count 1: kcount_cpu.cpp:75,348-352)
             if (WIDE) {
               atomicAdd(v + l, 1u);
               if (r < 4) atomicAdd(v + 5 + r, 1u);
@@ -275,30 +308,30 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             }
           } else {  // a contig instance: remembered as (occurrences, min depth, set of extension pairs), DESIGN.md "contig pass"
             atomicAdd(v + VR, 1u);
-            atomicMax(v + VR + 1, ~(mt2 & 0xFFFFu));
+            atomicMax(v + VR + 1, ~(hdr >> 16));
             atomicOr(v + VR + 2, 1u << (l * 5 + r));
           }
         }
-        __syncthreads();
+        const bool stop = group_barrier_or(grp, *(volatile u32 *)&s_over != 0);
         c0 += n_take;
         consumed += n_take;
-        if (s_over) {
-          over = true;
-          break;
-        }
+        if (stop) break;
         while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
       }
+      if (gt == 0 && consumed) atomicAdd(&s_consumed, consumed);
     }
     __syncthreads();
+    const bool over = s_over != 0;
     const bool wide_needed = !WIDE && s_wide;
     const u32 n = min(s_nkeys, a.key_cap);
     if (tid == 0) {
       ItemStatus st;
       st.overflow = over ? 1u : 0u;
-      st.progress = consumed;
+      st.progress = s_consumed;
       st.nkeys = n;
       st.wide = wide_needed ? 1u : 0u;
       a.status[item_idx] = st;
+      s_prev = n;
     }
     if (over || wide_needed) continue;
 

@@ -1,48 +1,51 @@
-// Stage A — parse: sequences -> supermers bucketed by (owner shard, partition).
+// Stage A — parse: sequences -> supermer records bucketed by (owner shard, partition).
 // Replaces SeqBlockInserter<MAX_K>::process_seq (reference src/kcount/kcount_cpu.cpp:73-103) together with
 // Kmer::get_kmers (kmer.cpp:155-257), get_minimizer_fast (kmer.cpp:345-393) and KmerDHT::get_kmer_target_rank
 // (kmer_dht.cpp:192-196) with O(1) work per k-mer. One THREAD per sequence (<= 256 bases; longer ones are tiled by the
 // host), 32 sequences per warp marching in lock step, every thread working in its own interleaved slice of shared memory
-// (word j of thread t at [j * blockDim + t]: conflict-free, no barriers anywhere):
+// (word j of thread t at [j * NT + t]: conflict-free, no barriers anywhere):
 //   1. 16-byte vector loads of the PackedRead bytes -> 2-bit codes (N -> G, kmer.cpp:169,187) + 1 "extension-valid" bit
 //      per base (high quality AND one of ACGT: kcount.cpp:81-84, kcount_cpu.cpp:157-164,320-323), 4 bases per multiply;
 //   2. phase A, one m-mer position per step: rolling forward / reverse-complement m-mer, canonical = min of the two
 //      (left-aligned u64), its position packed into the 10 free low bits; sliding-window MAX over w = k-m+1 positions
 //      = the minimizer of every k-mer, by the van Herk / Gil-Werman block decomposition (prefix maxima on the fly,
-//      suffix maxima rewritten once per block of w) — branch-free and identical control flow in all 32 lanes;
-//      each change of the window maximum appends (first k-mer, m-mer position) to a small per-thread list;
-//   3. phase B, once per <= 32 list entries, again converged across lanes: recompute that m-mer, bucket =
-//      (quick_hash(minimizer) % num_shards, partition from the high half of the same hash); a supermer = maximal run
-//      (<= 64 k-mers) of equal buckets over k-mers 1..len-k-1 (first and last k-mer are never counted,
-//      kcount_cpu.cpp:84-102); the thread appends {header, 2-bit bases, valid bits} to the bucket.
+//      suffix maxima rewritten once per block of w) — branch-free and identical control flow in all 32 lanes.
+//      Every change of the window maximum (value or position) starts a new supermer and appends (first k-mer, m-mer
+//      position) to a small per-thread list; a maximum lives at most w steps, so a supermer has <= w k-mers;
+//   3. phase B, per group of 4 list entries and converged across lanes: recompute the m-mer, bucket =
+//      (quick_hash(minimizer) % num_shards, partition from the high half of the same hash), reserve a record slot in
+//      the bucket (ONE 32-bit atomic), build the fixed-size record in registers and write it with 16-byte stores.
+// Supermer record = rw u32 words (rw % 4 == 0, 16-byte aligned; k=21: exactly 16 bytes):
+//      word 0: nb (bases, = k-mers + k + 1) | depth << 16     (depth: 1 for reads, contig depth for contig supermers)
+//      words 1 .. nwb: 2-bit bases, 16 per word, MSB first     (nwb = ceil(nb_max / 16), nb_max = w + k + 1)
+//      words 1+nwb .. : "extension-valid" bits, LSB first      (nwv = ceil(nb_max / 32))
+// Only k-mers 1..len-k-1 of a sequence are counted (first and last never are, kcount_cpu.cpp:84-102); supermer
+// boundaries are free to differ from the reference's.
 // The kernel runs twice per batch: COUNT (bucket histogram only) then FILL (exact-size buckets, no overflow possible).
 #pragma once
 #include "kc_device.cuh"
 
 namespace kc {
 
-struct BucketHist {  // per bucket, per batch; {nsup, nwords} is bumped by ONE 64-bit atomic
-  u32 nsup;    // supermers
-  u32 nwords;  // payload u32 words
-  u32 ninst;   // k-mer instances
-  u32 pad;
+struct BucketHist {  // per bucket, per batch; bumped by ONE 64-bit RED in COUNT, nsup is the 32-bit cursor in FILL
+  u32 nsup;   // supermers
+  u32 ninst;  // k-mer instances
 };
 
-struct BucketBase {  // FILL: where the bucket's headers / payload start
-  u64 hdr;
-  u64 pay;
+struct RecGeom {  // geometry of a supermer record for one k
+  int nb_max, nwb, nwv, rw;
 };
+__host__ __device__ inline RecGeom rec_geom(int k, int w) {
+  RecGeom g;
+  g.nb_max = w + k + 1;
+  g.nwb = (g.nb_max + 15) >> 4;
+  g.nwv = (g.nb_max + 31) >> 5;
+  g.rw = (1 + g.nwb + g.nwv + 3) & ~3;
+  return g;
+}
 
-struct SupHdr {   // 8 bytes per supermer
-  u32 woff;       // payload word offset inside the bucket's payload region
-  uint16_t nb;    // bases in the supermer (= k-mers + k + 1)
-  uint16_t depth; // 1 for reads; contig depth (kmer_count_t) for contig supermers (kmer_dht.hpp:78-91 Supermer::count)
-};
-
-constexpr int PARSE_TILE = 256;     // longest sequence one thread handles (positions fit 8 bits)
-constexpr int PARSE_LCAP = 32;      // list entries per thread between two phase-B drains
-constexpr int SUP_MAX_KMERS = 64;   // longest supermer, in k-mers (supermer boundaries are free to differ from the reference's)
-constexpr int PARSE_THREADS = 128;
+constexpr int PARSE_TILE = 256;  // longest sequence one thread handles (positions fit 8 bits)
+constexpr int PARSE_LCAP = 32;   // list entries per thread between two phase-B drains
 
 struct ParseArgs {
   const uint8_t *bytes;    // sequence bytes; sequence s occupies bytes[start, start+len)
@@ -56,10 +59,10 @@ struct ParseArgs {
   u32 qual_add;            // (0x80 - qual_cutoff) in every byte: SIMD "quality >= cutoff" test
   u32 num_shards, num_parts;  // partitions per shard (any number >= 1)
   int nsb, nsv;            // shared words per thread for bases / valid bits
+  int nwb, nwv, rw;        // record geometry
   BucketHist *hist;        // COUNT: += ; FILL: running cursors (start at 0)
-  const BucketBase *base;  // FILL
-  SupHdr *hdr;
-  u32 *payload;
+  const u64 *base;         // FILL: index of the bucket's first record
+  u32 *rec;                // FILL: records
   u64 *instances;          // += number of k-mer instances parsed
   u32 *err;                // |= 1 on a contig character outside ACGTNacgtn
 };
@@ -74,11 +77,11 @@ __device__ __forceinline__ u32 bucket_of(u64 minimizer, u32 num_shards, u32 num_
   return shard * num_parts + part;
 }
 
+template <int NT>
 struct Strided {  // thread-private array interleaved across the block
   u32 *p;
-  int stride;
-  __device__ __forceinline__ u32 operator[](int i) const { return p[i * stride]; }
-  __device__ __forceinline__ void set(int i, u32 v) const { p[i * stride] = v; }
+  __device__ __forceinline__ u32 operator[](int i) const { return p[i * NT]; }
+  __device__ __forceinline__ void set(int i, u32 v) const { p[i * NT] = v; }
 };
 
 // 16 PackedRead bytes (packed_reads.cpp:73-109: base 0..4 | min(qual,31) << 3) -> 16 2-bit codes MSB first + 16 valid bits
@@ -118,14 +121,14 @@ __device__ __forceinline__ void decode16_ascii(const uint4 v, int lo, int hi, u3
   }
 }
 
-template <bool FILL>
-__global__ void __launch_bounds__(PARSE_THREADS) parse_kernel(const ParseArgs a) {
+template <bool FILL, int NT>
+__global__ void __launch_bounds__(NT) parse_kernel(const ParseArgs a) {
   extern __shared__ __align__(16) u32 smem_parse[];
-  const int NT = blockDim.x, t = threadIdx.x;
-  const Strided sb{smem_parse + t, NT};                                    // [nsb] 2-bit bases, 16 per word, MSB first
-  const Strided sv{smem_parse + (size_t)a.nsb * NT + t, NT};               // [nsv] valid bits, LSB first
-  u64 *vh = (u64 *)(smem_parse + (size_t)(a.nsb + a.nsv) * NT) + t;        // [w] van Herk block: element j at vh[j*NT]
-  uint16_t *lst = (uint16_t *)(smem_parse + (size_t)(a.nsb + a.nsv + 2 * a.w) * NT) + t;  // [LCAP] entry e at lst[e*NT]
+  const int t = threadIdx.x;
+  const Strided<NT> sb{smem_parse + t};                                   // [nsb] 2-bit bases, 16 per word, MSB first
+  const Strided<NT> sv{smem_parse + a.nsb * NT + t};                      // [nsv] valid bits, LSB first
+  u64 *const vh = (u64 *)(smem_parse + (a.nsb + a.nsv) * NT) + t;         // [w] van Herk block: element j at vh[j*NT]
+  uint16_t *const lst = (uint16_t *)(smem_parse + (a.nsb + a.nsv + 2 * a.w) * NT) + t;  // [LCAP+1] entry e at lst[e*NT]
   const unsigned FULL = 0xffffffffu;
   const int k = a.k, m = a.m, w = a.w;
   const int msh = 64 - 2 * m;
@@ -179,76 +182,90 @@ __global__ void __launch_bounds__(PARSE_THREADS) parse_kernel(const ParseArgs a)
       sb.set(nwp + 2, 0);
       sv.set(nwp >> 1, 0);
       sv.set((nwp >> 1) + 1, 0);
-      for (int j = 0; j < w; j++) vh[(size_t)j * NT] = 0;
+      for (int j = 0; j < w; j++) vh[j * NT] = 0;
       nk = len - k - 1;  // k-mers i = 1..nk
       local_inst += (u32)nk;
     }
     const int nsteps = act ? nk + w - 1 : 0;  // m-mer positions p = 1..nsteps
     const int max_steps = __reduce_max_sync(FULL, nsteps);
 
-    // ---- state of the two phases ----
     u64 f = 0, r = 0, pmax = 0, last = ~0ULL;
     int j = 0, cnt = 0;
-    int run_i0 = 0;  // first k-mer of the open supermer (0 = none)
-    u32 run_b = 0;
     if (act) {
       f = fetch64(sb, a0) & mmask;  // m-mer at position 0; every step shifts in the base that completes position p
       r = revcomp64(f) << msh;
     }
 
-    auto emit_one = [&](int i0, int n_k, u32 b) {
-      const int nb = n_k + k + 1;
-      const int nwb = (nb + 15) >> 4, nwv = (nb + 31) >> 5;
-      const u64 inc = 1ULL | ((u64)(nwb + nwv) << 32);
-      if (!FILL) {
-        atomicAdd((u64 *)&a.hist[b], inc);
-        atomicAdd(&a.hist[b].ninst, (u32)n_k);
-      } else {
-        const u64 old = atomicAdd((u64 *)&a.hist[b], inc);
-        const u32 pos = (u32)old, wpos = (u32)(old >> 32);
-        const ulonglong2 bs = *(const ulonglong2 *)&a.base[b];
-        SupHdr h;
-        h.woff = wpos;
-        h.nb = (uint16_t)nb;
-        h.depth = (uint16_t)depth;
-        a.hdr[bs.x + pos] = h;
-        u32 *dst = a.payload + bs.y + wpos;
-        const int q0 = a0 + i0 - 1;
-        for (int x = 0; x < nwb; x++) dst[x] = (u32)(fetch64(sb, q0 + 16 * x) >> 32);
-        for (int x = 0; x < nwv; x++) {
-          const int qv = q0 + 32 * x;
-          dst[nwb + x] = __funnelshift_r(sv[qv >> 5], sv[(qv >> 5) + 1], qv & 31);
+    // phase B. Supermer e = k-mers [i_e, i_{e+1} - 1]; `fin`: the sequence is done, its last supermer ends at k-mer nk.
+    // Otherwise the last entry stays pending (moved to the front of the list) until the next one arrives.
+    auto drain = [&](bool fin) {
+      const int ndone = fin ? cnt : max(cnt - 1, 0);
+      const int maxd = __reduce_max_sync(FULL, ndone);
+      for (int e0 = 0; e0 < maxd; e0 += 4) {
+        u32 bkt[4], pos_[4], hdr_[4];
+        int i0_[4];
+        u64 base_[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int e = e0 + u;
+          bkt[u] = 0xFFFFFFFFu;
+          if (e < ndone) {
+            const u32 ent = lst[e * NT];
+            const int i0 = (int)(ent >> 8), mp = (int)(ent & 255u);
+            const int i1 = (e + 1 < cnt) ? (int)(lst[(e + 1) * NT] >> 8) - 1 : nk;
+            const int n_k = i1 - i0 + 1;
+            const u32 b = bucket_of(canonical_mmer(fetch64(sb, a0 + mp), m), a.num_shards, a.num_parts);
+            bkt[u] = b;
+            i0_[u] = i0;
+            hdr_[u] = (u32)(n_k + k + 1) | (depth << 16);
+            if (!FILL) {
+              atomicAdd((u64 *)&a.hist[b], 1ULL | ((u64)n_k << 32));
+            } else {
+              pos_[u] = atomicAdd(&a.hist[b].nsup, 1u);
+              base_[u] = __ldg(a.base + b);
+            }
+          }
         }
-      }
-    };
-    auto emit_run = [&](int i0, int i1, u32 b) {  // k-mers i0..i1, cut into supermers of <= SUP_MAX_KMERS k-mers
-      while (i0 <= i1) {
-        const int n = min(SUP_MAX_KMERS, i1 - i0 + 1);
-        emit_one(i0, n, b);
-        i0 += n;
-      }
-    };
-    auto drain = [&]() {  // phase B: converged across the warp, one list entry per lane and iteration
-      const int maxc = __reduce_max_sync(FULL, cnt);
-      for (int e = 0; e < maxc; e++) {
-        if (e < cnt) {
-          const u32 ent = lst[(size_t)e * NT];
-          const int i = (int)(ent >> 8), pos = (int)(ent & 255u);
-          const u32 b = bucket_of(canonical_mmer(fetch64(sb, a0 + pos), m), a.num_shards, a.num_parts);
-          if (run_i0 == 0) {
-            run_i0 = i;
-            run_b = b;
-          } else if (b != run_b) {
-            emit_run(run_i0, i - 1, run_b);
-            run_i0 = i;
-            run_b = b;
+        if (FILL) {
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            if (bkt[u] != 0xFFFFFFFFu) {
+              uint4 *dst = (uint4 *)(a.rec + (base_[u] + pos_[u]) * (u64)a.rw);
+              const int q0 = a0 + i0_[u] - 1;  // stream position of the supermer's first base (k-mer i0 - 1's first)
+              const int nb = (int)(hdr_[u] & 0xFFFFu);
+              const int nwb_s = (nb + 15) >> 4, nwv_s = (nb + 31) >> 5;  // words this supermer really fills
+              // word x of the record: 0 = header, 1..nwb = bases, then valid bits; unused words are zero
+              for (int x0 = 0; x0 < a.rw; x0 += 4) {
+                u32 wd[4];
+#pragma unroll
+                for (int y = 0; y < 4; y++) {
+                  const int x = x0 + y;
+                  u32 v = 0;
+                  if (x == 0) v = hdr_[u];
+                  else if (x <= a.nwb) {
+                    if (x - 1 < nwb_s) v = (u32)(fetch64(sb, q0 + 16 * (x - 1)) >> 32);
+                  } else if (x - 1 - a.nwb < nwv_s) {
+                    const int qv = q0 + 32 * (x - 1 - a.nwb);
+                    v = __funnelshift_r(sv[qv >> 5], sv[(qv >> 5) + 1], qv & 31);
+                  }
+                  wd[y] = v;
+                }
+                dst[x0 >> 2] = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+              }
+            }
           }
         }
       }
-      cnt = 0;
+      if (!fin && cnt > 0) {
+        lst[0] = lst[(cnt - 1) * NT];
+        cnt = 1;
+      } else {
+        cnt = 0;
+      }
     };
 
     // ---- 2. phase A ----
+    u64 *vh_j = vh;  // &vh[j * NT]
     for (int p = 1; p <= max_steps; p++) {
       if (p <= nsteps) {
         const u32 b = (u32)fetch_base(sb, a0 + p + m - 1);
@@ -258,37 +275,38 @@ __global__ void __launch_bounds__(PARSE_THREADS) parse_kernel(const ParseArgs a)
         pmax = (j == 0 || c > pmax) ? c : pmax;  // prefix maximum of the current block
         u64 mx = pmax;
         if (j < w - 1) {
-          const u64 sfx = vh[(size_t)(j + 1) * NT];  // suffix maximum of the previous block from offset j+1
+          const u64 sfx = vh_j[NT];  // suffix maximum of the previous block from offset j+1
           mx = sfx > mx ? sfx : mx;
         }
-        vh[(size_t)j * NT] = c;
+        *vh_j = c;
         if (p >= w && mx != last) {  // the window [p-w+1, p] is complete: k-mer i = p-w+1 has minimizer mx
           last = mx;
-          lst[(size_t)cnt * NT] = (uint16_t)(((u32)(p - w + 1) << 8) | ((u32)mx & 255u));
+          lst[cnt * NT] = (uint16_t)(((u32)(p - w + 1) << 8) | ((u32)mx & 255u));
           cnt++;
         }
       }
       if (j == w - 1) {  // end of a block (same step in every lane): turn it into suffix maxima in place
         if (p <= nsteps) {
-          u64 sfx = vh[(size_t)(w - 1) * NT];
+          u64 sfx = *vh_j;
           for (int jj = w - 2; jj >= 0; jj--) {
-            const u64 v = vh[(size_t)jj * NT];
+            const u64 v = vh[jj * NT];
             sfx = v > sfx ? v : sfx;
-            vh[(size_t)jj * NT] = sfx;
+            vh[jj * NT] = sfx;
           }
         }
         j = 0;
+        vh_j = vh;
       } else {
         j++;
+        vh_j += NT;
       }
-      if (__any_sync(FULL, cnt >= PARSE_LCAP)) drain();
+      if (__any_sync(FULL, cnt >= PARSE_LCAP)) drain(false);
     }
-    drain();
-    if (run_i0) emit_run(run_i0, nk, run_b);
+    drain(true);
   }
   if (bad) atomicOr(a.err, 1u);
   if (!FILL) {
-    const u32 tot = __reduce_add_sync(FULL, local_inst);  // < 2^32 per warp for any realistic launch (checked on the host)
+    const u32 tot = __reduce_add_sync(FULL, local_inst);  // < 2^32 per warp for any realistic launch
     if ((threadIdx.x & 31) == 0 && tot) atomicAdd(a.instances, (u64)tot);
   }
 }
