@@ -711,7 +711,6 @@ int finish_count(kc_handle *h) {
   ca.out_right = (char *)h->out_right.p;
   ca.out_cap = out_cap;
   ca.counters = (u64 *)d_counters.p;
-  ca.next_item = (u32 *)((u64 *)d_counters.p + 8);
   ca.pf_keys = h->cfg.keep_prefilter ? (u64 *)h->pf_keys.p : nullptr;
   ca.pf_vals = (uint16_t *)h->pf_vals.p;
   ca.pf_cap = pf_cap;
@@ -737,7 +736,6 @@ int finish_count(kc_handle *h) {
     RC(ensure(h, d_items, items.size() * sizeof(WorkItem)));
     RC(ensure(h, d_status, items.size() * sizeof(ItemStatus)));
     CK(cudaMemcpyAsync(d_items.p, items.data(), items.size() * sizeof(WorkItem), cudaMemcpyHostToDevice, h->s_main));
-    CK(cudaMemsetAsync(ca.next_item, 0, 4, h->s_main));
     ca.items = (const WorkItem *)d_items.p;
     ca.status = (ItemStatus *)d_status.p;
     ca.nitems = (u32)items.size();

@@ -68,7 +68,6 @@ struct CountArgs {
   const SegDesc *segs;
   ItemStatus *status;
   u32 nitems;
-  u32 *next_item;  // dynamic scheduler
   int k;
   int rw, nwb;     // record geometry (kc_parse.cuh)
   u32 tab_size, key_cap;  // tab_size u32 entries (multiple of 4)
@@ -123,7 +122,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   u32 *vals = (u32 *)(keys + (size_t)a.key_cap * KW);      // [key_cap * VW]
   SegDesc *segc = (SegDesc *)(vals + (size_t)a.key_cap * VW + ((a.key_cap * VW) & 1));  // [SEG_CACHE], 8-byte aligned
   __shared__ u64 s_obase[2];
-  __shared__ u32 s_item, s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed;
+  __shared__ __align__(16) WorkItem s_work;
+  __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed;
   __shared__ u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];
   __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -136,14 +136,26 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const u32 nbuckets = a.tab_size >> 2;
   const int sup_per_chunk = min(GRP_THREADS, GRP_STAGE_WORDS / rw);
   u32 my_max_probe = 0;
-  if (tid == 0) s_prev = a.key_cap;  // shared memory starts undefined: the first item clears every counter
+  // Work items are sorted heaviest first and dealt round-robin to the CTAs; the next item's descriptor is fetched while
+  // the current one is being processed.
+  if (tid == 0) {
+    s_prev = a.key_cap;  // shared memory starts undefined: the first item clears every counter
+    if (blockIdx.x < a.nitems) s_work = a.items[blockIdx.x];
+  }
 
-  for (;;) {
+  for (u32 item_idx = blockIdx.x; item_idx < a.nitems; item_idx += gridDim.x) {
     __syncthreads();
     const u32 prev = s_prev;
+    const WorkItem it = s_work;
+    const bool have_nx = tid == 0 && item_idx + gridDim.x < a.nitems;
+    uint4 nx0 = make_uint4(0, 0, 0, 0), nx1 = nx0;
+    if (have_nx) {
+      const uint4 *pn = (const uint4 *)(a.items + item_idx + gridDim.x);
+      nx0 = __ldg(pn);
+      nx1 = __ldg(pn + 1);
+    }
     __syncthreads();
     if (tid == 0) {
-      s_item = atomicAdd(a.next_item, 1u);
       s_nkeys = 0;
       s_over = 0;
       s_wide = 0;
@@ -153,9 +165,6 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
     for (u32 i = tid; i < nbuckets; i += CNT_THREADS) ((uint4 *)tab)[i] = make_uint4(0, 0, 0, 0);
     for (u32 i = tid; i < prev * VW; i += CNT_THREADS) vals[i] = 0;  // counters of the slots the previous item used
     __syncthreads();
-    const u32 item_idx = s_item;
-    if (item_idx >= a.nitems) break;
-    const WorkItem it = a.items[item_idx];
     const u32 nseg = it.seg_end - it.seg_begin;
 
     for (u32 sg0 = 0; sg0 < nseg; sg0 += SEG_CACHE) {
@@ -245,46 +254,48 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           }
           const u64 h = murmur64_words<KW>(key);  // Kmer::hash (kmer.cpp:465-468)
           if (it.nsub > 1 && ((u32)(h >> 40) & (it.nsub - 1)) != it.sub) continue;
-          // ---- find or claim ----
-          const u32 fp = (u32)(h >> 32) & ~IDX_MASK;
+          // ---- find or claim: one 128-bit load per bucket, everything else on registers ----
+          const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);  // never 0, so an empty entry never matches
           u32 bkt = __umulhi((u32)h, nbuckets);
           u32 mine = 0xFFFFFFFFu, idx = 0xFFFFFFFFu, probes = 0;
-          bool claimed = false, full = false;
+          bool claimed = false;
           for (;;) {
             const uint4 bq = lds128_volatile(tab + 4 * bkt);
-            u32 en4[4] = {bq.x, bq.y, bq.z, bq.w};
+            u32 mm = ((bq.x & ~IDX_MASK) == fp ? 1u : 0u) | ((bq.y & ~IDX_MASK) == fp ? 2u : 0u) |
+                     ((bq.z & ~IDX_MASK) == fp ? 4u : 0u) | ((bq.w & ~IDX_MASK) == fp ? 8u : 0u);
+            while (mm) {  // almost always exactly one candidate, and it is the key
+              const u32 en = (mm & 1u) ? bq.x : (mm & 2u) ? bq.y : (mm & 4u) ? bq.z : bq.w;
+              const u32 cand = (en & IDX_MASK) - 1u;
+              bool same = true;
 #pragma unroll
-            for (int q = 0; q < 4; q++) {
-              if (idx != 0xFFFFFFFFu || full) break;
-              u32 en = en4[q];
-              if (en == 0) {
-                if (mine == 0xFFFFFFFFu) {  // reserve a dense entry, fill it, then publish it
-                  mine = atomicAdd(&s_nkeys, 1u);
-                  if (mine >= a.key_cap) {
-                    s_over = 1;
-                    full = true;
-                    break;
-                  }
-#pragma unroll
-                  for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
-                  __threadfence_block();
-                }
-                en = atomicCAS(&tab[4 * bkt + q], 0u, fp | (mine + 1u));
-                if (en == 0) {
-                  idx = mine;
-                  claimed = true;
+              for (int i = 0; i < KW; i++) same = same && (((volatile u64 *)keys)[(size_t)cand * KW + i] == key[i]);
+              if (same) {
+                idx = cand;
+                break;
+              }
+              mm &= mm - 1u;
+            }
+            if (idx != 0xFFFFFFFFu) break;
+            const u32 em = (bq.x == 0 ? 1u : 0u) | (bq.y == 0 ? 2u : 0u) | (bq.z == 0 ? 4u : 0u) | (bq.w == 0 ? 8u : 0u);
+            if (em) {  // the key is not in the table (entries are never removed): claim the bucket's first empty entry
+              if (mine == 0xFFFFFFFFu) {  // reserve a dense entry, fill it, then publish it
+                mine = atomicAdd(&s_nkeys, 1u);
+                if (mine >= a.key_cap) {
+                  s_over = 1;
                   break;
                 }
-              }
-              if ((en & ~IDX_MASK) == fp) {
-                const u32 cand = (en & IDX_MASK) - 1u;
-                bool same = true;
 #pragma unroll
-                for (int i = 0; i < KW; i++) same = same && (((volatile u64 *)keys)[(size_t)cand * KW + i] == key[i]);
-                if (same) idx = cand;
+                for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
+                __threadfence_block();
               }
+              const u32 q = (u32)__ffs(em) - 1u;
+              if (atomicCAS(&tab[4 * bkt + q], 0u, fp | (mine + 1u)) == 0u) {
+                idx = mine;
+                claimed = true;
+                break;
+              }
+              continue;  // somebody else took that entry: look at this bucket again (it may now hold our key)
             }
-            if (idx != 0xFFFFFFFFu || full) break;
             probes++;
             bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
           }
@@ -332,6 +343,10 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       st.wide = wide_needed ? 1u : 0u;
       a.status[item_idx] = st;
       s_prev = n;
+      if (have_nx) {
+        ((uint4 *)&s_work)[0] = nx0;
+        ((uint4 *)&s_work)[1] = nx1;
+      }
     }
     if (over || wide_needed) continue;
 

@@ -169,13 +169,20 @@ class KmerCounter:
         self._ck(self.lib.kc_num_survivors(self.h, C.byref(n)), "kc_num_survivors")
         return n.value
 
+    def survivors_into(self, keys_ptr, counts_ptr, left_ptr, right_ptr):
+        """Copy the surviving table into caller-owned HOST buffers (raw pointers, e.g. pinned memory); returns n."""
+        n = self.num_survivors()
+        self._ck(self.lib.kc_copy_survivors(self.h, C.c_void_p(keys_ptr), C.c_void_p(counts_ptr), C.c_void_p(left_ptr),
+                                            C.c_void_p(right_ptr)), "kc_copy_survivors")
+        return n
+
     def survivors(self, sort=True):
         """(keys[n, n_longs] u64, counts u16, left u8 chars, right u8 chars); sorted by key words when sort=True."""
         n = self.num_survivors()
-        keys = np.zeros((n, self.n_longs), dtype=np.uint64)
-        counts = np.zeros(n, dtype=np.uint16)
-        left = np.zeros(n, dtype=np.uint8)
-        right = np.zeros(n, dtype=np.uint8)
+        keys = np.empty((n, self.n_longs), dtype=np.uint64)
+        counts = np.empty(n, dtype=np.uint16)
+        left = np.empty(n, dtype=np.uint8)
+        right = np.empty(n, dtype=np.uint8)
         self._ck(self.lib.kc_copy_survivors(self.h, _ptr(keys), _ptr(counts), _ptr(left), _ptr(right)), "kc_copy_survivors")
         if sort and n:
             order = np.lexsort([keys[:, j] for j in range(self.n_longs - 1, -1, -1)])
