@@ -292,6 +292,27 @@ void decide_partitions(kc_handle *h, u64 inst_estimate) {
   h->st.num_partitions = h->P;
 }
 
+// exclusive prefix sum of the per-bucket supermer counts -> index of each bucket's first record (one block; n is 10^5..10^6)
+__global__ void __launch_bounds__(1024) bucket_scan_kernel(const BucketHist *hist, u32 n, u64 *base) {
+  __shared__ u64 part[1024];
+  const u32 per = (n + 1023) / 1024, lo = threadIdx.x * per, hi = min(n, lo + per);
+  u64 sum = 0;
+  for (u32 i = lo; i < hi; i++) sum += hist[i].nsup;
+  part[threadIdx.x] = sum;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const u64 v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  u64 run = part[threadIdx.x] - sum;
+  for (u32 i = lo; i < hi; i++) {
+    base[i] = run;
+    run += hist[i].nsup;
+  }
+}
+
 // Parse one batch that is already on the device. `bytes` may be a virtual base (bytes + start always lands inside
 // the staged range). Either offsets (direct mode) or seg_* (segment mode) is given.
 int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, const u64 *d_seg_start, const u32 *d_seg_len,
@@ -350,6 +371,10 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
   CK(cudaEventRecord(h->ev_c, h->s_main));
+  // bucket layout on the device (FILL must not wait for a host round trip: a small H2D copy would queue behind the bulk
+  // copy of the next batch of reads); the host computes the same prefix for its own bookkeeping
+  bucket_scan_kernel<<<1, 1024, 0, h->s_main>>>((const BucketHist *)h->d_hist.p, NP, (u64 *)h->d_base.p);
+  h->st.gpu_launches++;
   Block blk;
   blk.is_ctg = is_ctg;
   blk.hist.resize(NP);
@@ -369,7 +394,6 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   }
   const size_t rec_bytes = (size_t)hs * a.rw * 4;
   CK(dev_alloc((void **)&blk.rec, rec_bytes + 64));
-  CK(cudaMemcpyAsync(h->d_base.p, blk.rec_base.data(), sizeof(u64) * NP, cudaMemcpyHostToDevice, h->s_main));
   CK(cudaMemsetAsync(h->d_cursor.p, 0, sizeof(BucketHist) * NP, h->s_main));
   // FILL
   a.hist = (BucketHist *)h->d_cursor.p;
@@ -465,21 +489,19 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
   if (!bytes || !offsets) return fail(h, KC_ERR_INVALID, "null input");
   CK(cudaSetDevice(h->cfg.device));
   const int k = h->cfg.kmer_len;
-  u64 max_len = 0, inst = 0;
-  for (u64 r = 0; r < n_reads; r++) {
-    const u64 l = offsets[r + 1] - offsets[r];
-    max_len = std::max(max_len, l);
-    if (l >= (u64)k + 2) inst += l - k - 1;
+  {  // instances ~ bases - reads * (k + 1); exact when every read has at least k + 1 bases (only sizes the partitions)
+    const u64 bases = offsets[n_reads] - offsets[0], k1 = (u64)k + 1;
+    decide_partitions(h, bases > n_reads * k1 ? bases - n_reads * k1 : 0);
   }
-  decide_partitions(h, inst);
-  const bool tiled = max_len > (u64)SEG_MAX;
-  u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : (4ull << 20);
+  u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : (2ull << 20);
   const u64 avg = std::max<u64>(1, (offsets[n_reads] - offsets[0]) / n_reads);
   batch = std::max<u64>(1, std::min<u64>(batch, (1ull << 30) / avg));  // <= ~1 GB of bases per batch
   const u64 nb = (n_reads + batch - 1) / batch;
-  cudaEvent_t t0, t1;
-  CK(cudaEventCreate(&t0));
-  CK(cudaEventCreate(&t1));
+  cudaEvent_t t0[2], t1[2];
+  for (int i = 0; i < 2; i++) {
+    CK(cudaEventCreate(&t0[i]));
+    CK(cudaEventCreate(&t1[i]));
+  }
   float ms_copy = 0;
   auto issue_copy = [&](u64 bi) -> int {
     const int sl = (int)(bi & 1);
@@ -488,12 +510,11 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
     CK(cudaEventSynchronize(h->ev_free[sl]));  // the parse that last used this stage has finished
     RC(ensure(h, h->stage_bytes[sl], b1 - b0 + 64));
     RC(ensure(h, h->stage_offs[sl], (r1 - r0 + 1) * 8));
-    CK(cudaEventRecord(t0, h->s_copy));
+    CK(cudaEventRecord(t0[sl], h->s_copy));
     CK(cudaMemcpyAsync(h->stage_bytes[sl].p, bytes + b0, b1 - b0, cudaMemcpyHostToDevice, h->s_copy));
     CK(cudaMemcpyAsync(h->stage_offs[sl].p, offsets + r0, (r1 - r0 + 1) * 8, cudaMemcpyHostToDevice, h->s_copy));
-    CK(cudaEventRecord(t1, h->s_copy));
+    CK(cudaEventRecord(t1[sl], h->s_copy));
     CK(cudaEventRecord(h->ev_copy[sl], h->s_copy));
-    h->st.supermer_bytes_sent += 0;
     return KC_OK;
   };
   int rc = issue_copy(0);
@@ -501,13 +522,16 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
   for (u64 bi = 0; bi < nb; bi++) {
     const int sl = (int)(bi & 1);
     const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
-    CK(cudaEventSynchronize(h->ev_copy[sl]));
-    ms_copy += elapsed(t0, t1);
     if (bi + 1 < nb) {  // next batch's copy overlaps this batch's parse
       rc = issue_copy(bi + 1);
       if (rc) return rc;
     }
     const uint8_t *vbase = (const uint8_t *)h->stage_bytes[sl].p - offsets[r0];
+    u64 max_len = 0;  // scanned while the copies are in flight
+    for (u64 r = r0; r < r1; r++) max_len = std::max<u64>(max_len, offsets[r + 1] - offsets[r]);
+    const bool tiled = max_len > (u64)SEG_MAX;
+    CK(cudaEventSynchronize(h->ev_copy[sl]));
+    ms_copy += elapsed(t0[sl], t1[sl]);
     if (!tiled) {
       rc = parse_batch(h, vbase, (const u64 *)h->stage_offs[sl].p, nullptr, nullptr, nullptr, r1 - r0, (int)max_len, false, false);
     } else {
@@ -520,8 +544,10 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
     if (rc) return rc;
     CK(cudaEventRecord(h->ev_free[sl], h->s_main));
   }
-  cudaEventDestroy(t0);
-  cudaEventDestroy(t1);
+  for (int i = 0; i < 2; i++) {
+    cudaEventDestroy(t0[i]);
+    cudaEventDestroy(t1[i]);
+  }
   h->st.ms_h2d += ms_copy;
   h->st.num_seqs += n_reads;
   h->st.num_bases += offsets[n_reads] - offsets[0];
