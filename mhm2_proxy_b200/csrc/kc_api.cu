@@ -34,14 +34,24 @@ struct DevBuf {
 // one parsed batch (or one received batch): supermers of every bucket laid out bucket-major
 struct Block {
   u32 *rec = nullptr;            // supermer records, rw words each, bucket-major
-  std::vector<BucketHist> hist;  // per bucket of the PRODUCER (num_shards*P) for local blocks; P entries for received
-  std::vector<u64> rec_base;     // index of each bucket's first record (+ total at the end)
+  BucketHist *d_hist = nullptr;  // device: supermers and k-mer instances per bucket (also the directory sent to peers)
+  u64 *d_base = nullptr;         // device: index of each bucket's first record (exclusive scan of d_hist[].nsup)
+  // d_hist / d_base cover the PRODUCER's buckets (num_shards * P) for local blocks, P entries for received ones
+  std::vector<u64> dest_base;    // host, local blocks: first record of each destination shard's range (+ total at the end)
   u64 tot_sup = 0;
   bool is_ctg = false;
   bool received = false;  // true: indexed by partition only
 };
 
 struct Nccl;  // opaque, kc_comm.inl
+
+// a receive posted by an exchange round: becomes a received Block once its directory is back on the host (kc_comm.inl)
+struct Pending {
+  BucketHist *dir = nullptr;  // P entries, device
+  u32 *rec = nullptr;
+  u64 nsup = 0;
+  bool is_ctg = false;
+};
 
 }  // namespace
 
@@ -52,12 +62,17 @@ struct kc_handle {
   RecGeom geom;  // supermer record geometry for this k
   u32 P = 0;  // partitions per shard (0 until the first add decides)
   bool finished = false, has_ctg = false;
-  cudaStream_t s_main = nullptr, s_copy = nullptr;
+  cudaStream_t s_main = nullptr, s_copy = nullptr, s_comm = nullptr;
+  std::vector<Pending> pending;
+  DevBuf d_meta, d_meta_all, d_tot;
+  u64 *h_pin = nullptr;  // pinned scratch (PIN_BYTES): [0, PIN_META) bucket totals / counters, [PIN_META, ..) exchange metadata
+  size_t pin_bytes = 0;
+  cudaEvent_t ev_fill = nullptr, ev_x0 = nullptr, ev_x1 = nullptr;
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
   std::vector<Block> blocks;       // produced locally
   std::vector<Block> rblocks;      // received from peers (multi-shard)
   DevBuf stage_bytes[2], stage_offs[2];
-  DevBuf d_hist, d_cursor, d_base, d_misc;  // d_misc: u64 instances, u32 err
+  DevBuf d_cursor, d_misc;  // d_misc: u64 instances, u32 err
   // outputs
   DevBuf out_keys, out_counts, out_left, out_right, pf_keys, pf_vals;
   u64 n_surv = 0, n_pf = 0;
@@ -67,6 +82,8 @@ struct kc_handle {
 };
 
 namespace {
+
+int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done);  // kc_comm.inl
 
 int fail(kc_handle *h, int code, const char *fmt, ...) {
   char buf[512];
@@ -212,6 +229,42 @@ extern "C" void kc_config_default(kc_config *cfg, int32_t kmer_len) {
 
 extern "C" const char *kc_last_error(const kc_handle *h) { return h ? h->err.c_str() : "null handle"; }
 
+namespace {
+
+// pinned host scratch, pooled process-wide (cudaMallocHost / cudaFreeHost cost far more than a kcount round can afford)
+constexpr size_t PIN_META = 4096;
+struct PinPool {
+  std::mutex mu;
+  std::multimap<size_t, void *> free_blocks;
+};
+PinPool &pin_pool() {
+  static PinPool p;
+  return p;
+}
+cudaError_t pin_get(void **p, size_t &bytes) {
+  bytes = std::max<size_t>(bytes, 64 << 10);
+  PinPool &pp = pin_pool();
+  {
+    std::lock_guard<std::mutex> lk(pp.mu);
+    auto it = pp.free_blocks.lower_bound(bytes);
+    if (it != pp.free_blocks.end()) {
+      *p = it->second;
+      bytes = it->first;
+      pp.free_blocks.erase(it);
+      return cudaSuccess;
+    }
+  }
+  return cudaMallocHost(p, bytes);
+}
+void pin_put(void *p, size_t bytes) {
+  if (!p) return;
+  PinPool &pp = pin_pool();
+  std::lock_guard<std::mutex> lk(pp.mu);
+  pp.free_blocks.emplace(bytes, p);
+}
+
+}  // namespace
+
 extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   if (!cfg || !out) return KC_ERR_INVALID;
   *out = nullptr;
@@ -241,6 +294,10 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   CK(cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, cfg->device));
   CK(cudaStreamCreateWithFlags(&h->s_main, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&h->s_comm, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&h->ev_fill, cudaEventDisableTiming));
+  CK(cudaEventCreate(&h->ev_x0));
+  CK(cudaEventCreate(&h->ev_x1));
   CK(cudaEventCreate(&h->ev_a));
   CK(cudaEventCreate(&h->ev_b));
   CK(cudaEventCreate(&h->ev_c));
@@ -251,6 +308,9 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   }
   RC(ensure(h, h->d_misc, 64));
   CK(cudaMemsetAsync(h->d_misc.p, 0, 64, h->s_main));
+  h->pin_bytes = PIN_META + ((size_t)cfg->num_shards + 3) * (size_t)cfg->num_shards * 8;
+  if ((size_t)(cfg->num_shards + 1) * 8 > PIN_META) return fail(h, KC_ERR_INVALID, "num_shards %d too large", cfg->num_shards);
+  CK(pin_get((void **)&h->h_pin, h->pin_bytes));
   return KC_OK;
 }
 
@@ -292,10 +352,11 @@ void decide_partitions(kc_handle *h, u64 inst_estimate) {
   h->st.num_partitions = h->P;
 }
 
-// exclusive prefix sum of the per-bucket supermer counts -> index of each bucket's first record (one block; n is 10^5..10^6)
-__global__ void __launch_bounds__(1024) bucket_scan_kernel(const BucketHist *hist, u32 n, u64 *base) {
+// exclusive prefix sum of the per-bucket supermer counts -> index of each bucket's first record (one block; n is 10^5..10^6).
+// totals (optional): the first record of every destination shard's range, totals[n / P] = all of them
+__global__ void __launch_bounds__(1024) bucket_scan_kernel(const BucketHist *hist, u32 n, u64 *base, u32 P, u64 *totals) {
   __shared__ u64 part[1024];
-  const u32 per = (n + 1023) / 1024, lo = threadIdx.x * per, hi = min(n, lo + per);
+  const u32 per = (n + 1023) / 1024, lo = min(n, threadIdx.x * per), hi = min(n, lo + per);
   u64 sum = 0;
   for (u32 i = lo; i < hi; i++) sum += hist[i].nsup;
   part[threadIdx.x] = sum;
@@ -309,8 +370,10 @@ __global__ void __launch_bounds__(1024) bucket_scan_kernel(const BucketHist *his
   u64 run = part[threadIdx.x] - sum;
   for (u32 i = lo; i < hi; i++) {
     base[i] = run;
+    if (totals && i % P == 0) totals[i / P] = run;
     run += hist[i].nsup;
   }
+  if (totals && threadIdx.x == 1023) totals[n / P] = part[1023];
 }
 
 // Parse one batch that is already on the device. `bytes` may be a virtual base (bytes + start always lands inside
@@ -319,9 +382,9 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
                 const uint16_t *d_seg_depth, u64 nseq, int max_len, bool ascii, bool is_ctg) {
   if (nseq == 0) return KC_OK;
   const u32 NP = h->P * (u32)h->cfg.num_shards;
-  RC(ensure(h, h->d_hist, sizeof(BucketHist) * NP));
+  const int N = h->cfg.num_shards;
   RC(ensure(h, h->d_cursor, sizeof(BucketHist) * NP));
-  RC(ensure(h, h->d_base, sizeof(u64) * NP));
+  RC(ensure(h, h->d_tot, sizeof(u64) * (size_t)(N + 1)));
   ParseArgs a;
   memset(&a, 0, sizeof(a));
   a.bytes = d_bytes;
@@ -364,32 +427,29 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
   // COUNT
-  CK(cudaMemsetAsync(h->d_hist.p, 0, sizeof(BucketHist) * NP, h->s_main));
-  a.hist = (BucketHist *)h->d_hist.p;
+  Block blk;
+  blk.is_ctg = is_ctg;
+  CK(dev_alloc((void **)&blk.d_hist, sizeof(BucketHist) * NP));
+  CK(cudaMemsetAsync(blk.d_hist, 0, sizeof(BucketHist) * NP, h->s_main));
+  a.hist = blk.d_hist;
   k_count<<<grid, threads, smem, h->s_main>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
   CK(cudaEventRecord(h->ev_c, h->s_main));
-  // bucket layout on the device (FILL must not wait for a host round trip: a small H2D copy would queue behind the bulk
-  // copy of the next batch of reads); the host computes the same prefix for its own bookkeeping
-  bucket_scan_kernel<<<1, 1024, 0, h->s_main>>>((const BucketHist *)h->d_hist.p, NP, (u64 *)h->d_base.p);
+  // bucket layout on the device: the host only needs the totals (allocation size, the range that goes to each shard)
+  CK(dev_alloc((void **)&blk.d_base, sizeof(u64) * NP));
+  bucket_scan_kernel<<<1, 1024, 0, h->s_main>>>(blk.d_hist, NP, blk.d_base, h->P, (u64 *)h->d_tot.p);
   h->st.gpu_launches++;
-  Block blk;
-  blk.is_ctg = is_ctg;
-  blk.hist.resize(NP);
-  CK(cudaMemcpyAsync(blk.hist.data(), h->d_hist.p, sizeof(BucketHist) * NP, cudaMemcpyDeviceToHost, h->s_main));
+  CK(cudaMemcpyAsync(h->h_pin, h->d_tot.p, sizeof(u64) * (size_t)(N + 1), cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
-  blk.rec_base.resize(NP + 1);
-  u64 hs = 0;
-  for (u32 b = 0; b < NP; b++) {
-    blk.rec_base[b] = hs;
-    hs += blk.hist[b].nsup;
-  }
-  blk.rec_base[NP] = hs;
+  blk.dest_base.assign(h->h_pin, h->h_pin + N + 1);
+  const u64 hs = blk.dest_base[N];
   blk.tot_sup = hs;
   if (hs == 0) {
     CK(cudaEventRecord(e1, h->s_main));
+    dev_free(blk.d_hist);
+    dev_free(blk.d_base);
     return KC_OK;
   }
   const size_t rec_bytes = (size_t)hs * a.rw * 4;
@@ -397,7 +457,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   CK(cudaMemsetAsync(h->d_cursor.p, 0, sizeof(BucketHist) * NP, h->s_main));
   // FILL
   a.hist = (BucketHist *)h->d_cursor.p;
-  a.base = (const u64 *)h->d_base.p;
+  a.base = blk.d_base;
   a.rec = blk.rec;
   CK(cudaEventRecord(h->ev_d, h->s_main));
   k_fill<<<grid, threads, smem, h->s_main>>>(a);
@@ -405,7 +465,12 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
   CK(cudaEventRecord(e1, h->s_main));
-  CK(cudaStreamSynchronize(h->s_main));  // rec_base is about to move; also surfaces kernel faults here
+  CK(cudaEventRecord(h->ev_fill, h->s_main));
+  if (h->comm) {  // multi-shard with NCCL: this batch's supermers leave now, while the next batch is copied in and parsed
+    int rcx = exchange_round(h, &blk, false, nullptr);
+    if (rcx) return rcx;
+  }
+  CK(cudaStreamSynchronize(h->s_main));  // also surfaces kernel faults here
   h->st.ms_parse += elapsed(e0, e1);
   h->st.ms_parse_count += elapsed(e0, h->ev_c);
   h->st.ms_parse_fill += elapsed(h->ev_d, e1);
@@ -427,7 +492,7 @@ extern "C" int kc_add_reads_device(kc_handle *h, const uint8_t *d_bytes, const u
   CK(cudaSetDevice(h->cfg.device));
   const u64 k1 = (u64)h->cfg.kmer_len + 1;
   decide_partitions(h, total_bytes > n_reads * k1 ? total_bytes - n_reads * k1 : 0);
-  const u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : (8ull << 20);
+  const u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : h->comm ? (4ull << 20) : (8ull << 20);  // with peers: a batch is the unit that overlaps its exchange with the next parse
   for (u64 r0 = 0; r0 < n_reads; r0 += batch) {
     const u64 n = std::min<u64>(batch, n_reads - r0);
     int rc = parse_batch(h, d_bytes, (const u64 *)d_offsets + r0, nullptr, nullptr, nullptr, n, (int)max_read_len, false, false);
@@ -660,11 +725,11 @@ extern "C" int kc_finish(kc_handle *h) {
   if (!h) return KC_ERR_INVALID;
   if (h->finished) return fail(h, KC_ERR_STATE, "finish called twice");
   CK(cudaSetDevice(h->cfg.device));
-  if (!h->P) decide_partitions(h, 0);
   if (h->cfg.num_shards > 1) {
     int rc = kc_exchange(h);
     if (rc) return rc;
   }
+  if (!h->P) decide_partitions(h, 0);
   return finish_count(h);
 }
 
@@ -675,52 +740,68 @@ int finish_count(kc_handle *h) {
   const u32 P = h->P;
   const int KW = h->KW;
   const u32 me = (u32)h->cfg.shard_id;
-  // every run of supermers that belongs to this shard, partition-major
-  std::vector<const Block *> blks;
-  std::vector<u32> first_bucket;
+  // every batch that holds supermers of this shard: own buckets of the locally parsed ones, all of the received ones
+  std::vector<BlockDesc> descs;
   bool any_ctg = false;
-  for (auto &b : h->blocks)
-    if (b.tot_sup) { blks.push_back(&b); first_bucket.push_back(me * P); any_ctg |= b.is_ctg; }
-  for (auto &b : h->rblocks)
-    if (b.tot_sup) { blks.push_back(&b); first_bucket.push_back(0); any_ctg |= b.is_ctg; }
-  std::vector<SegDesc> hsegs;
-  std::vector<WorkItem> items;
-  hsegs.reserve((size_t)P * std::max<size_t>(blks.size(), 1));
-  items.reserve(P);
-  u64 read_inst = 0, ctg_inst = 0, tot_sup = 0;
-  for (u32 p = 0; p < P; p++) {
-    WorkItem it;
-    memset(&it, 0, sizeof(it));
-    it.seg_begin = (u32)hsegs.size();
-    u64 nsup = 0;
-    for (size_t bi = 0; bi < blks.size(); bi++) {
-      const Block &b = *blks[bi];
-      const u32 bu = first_bucket[bi] + p;
-      if (!b.hist[bu].nsup) continue;
-      SegDesc sd;
-      sd.rec = b.rec + (size_t)b.rec_base[bu] * h->geom.rw;
-      sd.nsup = b.hist[bu].nsup;
-      sd.is_ctg = b.is_ctg ? 1 : 0;
-      sd.sup0 = (u32)nsup;
-      sd.pad = 0;
-      nsup += sd.nsup;
-      (b.is_ctg ? ctg_inst : read_inst) += b.hist[bu].ninst;
-      hsegs.push_back(sd);
-    }
-    if (!nsup) continue;
-    if (nsup > 0xFFFFFFF0ull) return fail(h, KC_ERR_INVALID, "partition %u holds too many supermers: use more partitions", p);
-    it.seg_end = (u32)hsegs.size();
-    it.nsup = (u32)nsup;
-    it.part = p;
-    it.sub = 0;
-    it.nsub = 1;
-    tot_sup += nsup;
-    items.push_back(it);
+  u64 sup_expected = 0;
+  for (auto &b : h->blocks) {
+    const u64 mine = b.tot_sup ? b.dest_base[me + 1] - b.dest_base[me] : 0;
+    if (!mine) continue;
+    descs.push_back(BlockDesc{b.rec, b.d_hist, b.d_base, me * P, b.is_ctg ? 1u : 0u});
+    any_ctg |= b.is_ctg;
+    sup_expected += mine;
   }
-  ht.lap("finish: build items/segs");
+  for (auto &b : h->rblocks) {
+    if (!b.tot_sup) continue;
+    descs.push_back(BlockDesc{b.rec, b.d_hist, b.d_base, 0u, b.is_ctg ? 1u : 0u});
+    any_ctg |= b.is_ctg;
+    sup_expected += b.tot_sup;
+  }
+  const u32 nblk = (u32)descs.size();
+  if ((u64)P * std::max(nblk, 1u) > 0xFFFFFFF0ull) return fail(h, KC_ERR_INVALID, "too many batches (%u) for %u partitions", nblk, P);
+  // work items and their segment lists are built on the device, where the bucket directories are (kc_count.cuh)
+  DevBuf d_counters, d_segs, d_items, d_status, d_descs, d_heavy;
+  RC(ensure(h, d_counters, CTR_WORDS * 8));
+  CK(cudaMemsetAsync(d_counters.p, 0, CTR_WORDS * 8, h->s_main));
+  RC(ensure(h, d_segs, (size_t)P * std::max(nblk, 1u) * sizeof(SegDesc) + 64));
+  RC(ensure(h, d_items, (size_t)P * sizeof(WorkItem)));
+  RC(ensure(h, d_status, (size_t)P * sizeof(ItemStatus)));
+  RC(ensure(h, d_heavy, (size_t)P * 8));
+  RC(ensure(h, d_descs, std::max<size_t>(nblk, 1) * sizeof(BlockDesc)));
+  if (nblk) CK(cudaMemcpyAsync(d_descs.p, descs.data(), nblk * sizeof(BlockDesc), cudaMemcpyHostToDevice, h->s_main));
+  CK(cudaMemsetAsync(d_status.p, 0, (size_t)P * sizeof(ItemStatus), h->s_main));
+  BuildArgs ba;
+  ba.blocks = (const BlockDesc *)d_descs.p;
+  ba.nblk = nblk;
+  ba.P = P;
+  ba.rw = h->geom.rw;
+  // Hash partitions are statistically alike; only outliers (skewed data: heavy-hitter partitions) are scheduled ahead
+  ba.heavy_thr = 2 * (sup_expected / P) + 1;
+  ba.segs = (SegDesc *)d_segs.p;
+  ba.items = (WorkItem *)d_items.p;
+  ba.heavy = (u64 *)d_heavy.p;
+  ba.counters = (u64 *)d_counters.p;
+  build_items_kernel<<<(P + 255) / 256, 256, 0, h->s_main>>>(ba);
+  h->st.gpu_launches++;
+  CK(cudaGetLastError());
+  u64 *ctr = h->h_pin;  // pinned
+  CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
+  if (ctr[CTR_ERR]) return fail(h, KC_ERR_INVALID, "a partition holds too many supermers: use more partitions");
+  const u64 read_inst = ctr[CTR_READ_INST], ctg_inst = ctr[CTR_CTG_INST];
+  u32 n_heavy = (u32)ctr[CTR_NHEAVY];
+  if (ctr[CTR_SUP] != sup_expected) return fail(h, KC_ERR_CUDA, "internal: bucket directories do not add up");
+  if (n_heavy) {  // heaviest first
+    std::vector<u64> hv(n_heavy);
+    CK(cudaMemcpy(hv.data(), d_heavy.p, (size_t)n_heavy * 8, cudaMemcpyDeviceToHost));
+    std::sort(hv.begin(), hv.end(), [](u64 x, u64 y) { return x > y; });
+    CK(cudaMemcpyAsync(d_heavy.p, hv.data(), (size_t)n_heavy * 8, cudaMemcpyHostToDevice, h->s_main));
+    CK(cudaStreamSynchronize(h->s_main));
+  }
+  ht.lap("finish: build items/segs (device)");
   h->st.instances_inserted = read_inst + ctg_inst;
   h->st.ctg_instances_inserted = ctg_inst;
-  h->st.supermers_in = tot_sup;
+  h->st.supermers_in = sup_expected;
 
   // outputs: a k-mer needs count >= 2 to survive, so survivors <= read instances / 2 + contig instances
   const u64 out_cap = read_inst / 2 + ctg_inst + 1024;
@@ -734,11 +815,6 @@ int finish_count(kc_handle *h) {
     RC(ensure(h, h->pf_keys, pf_cap * KW * 8));
     RC(ensure(h, h->pf_vals, pf_cap * 18));
   }
-  DevBuf d_counters, d_segs, d_items, d_status;
-  RC(ensure(h, d_counters, 128));
-  CK(cudaMemsetAsync(d_counters.p, 0, 128, h->s_main));
-  RC(ensure(h, d_segs, hsegs.size() * sizeof(SegDesc) + 64));
-  if (!hsegs.empty()) CK(cudaMemcpyAsync(d_segs.p, hsegs.data(), hsegs.size() * sizeof(SegDesc), cudaMemcpyHostToDevice, h->s_main));
 
   CountArgs ca;
   memset(&ca, 0, sizeof(ca));
@@ -758,103 +834,113 @@ int finish_count(kc_handle *h) {
   ca.pf_vals = (uint16_t *)h->pf_vals.p;
   ca.pf_cap = pf_cap;
 
-  ht.lap("finish: alloc + seg upload");
+  ht.lap("finish: output buffers");
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
+  // Round 0 runs the device-built items. Items that report trouble come back to the host: a full key store is re-run as
+  // 2^n hash sub-passes, a wrapped u16 counter is re-run with u32 counters.
+  std::vector<WorkItem> items, wide_items;  // host copies exist only for retry rounds
   std::vector<ItemStatus> status;
-  std::vector<WorkItem> wide_items;
-  bool wide = false;
+  bool wide = false, first = true;
+  u64 retries_seen = 0;
   int round = 0;
-  while (!items.empty() || !wide_items.empty()) {
-    if (items.empty()) {  // narrow rounds are done: re-run the items whose u16 counters wrapped with u32 counters
+  DevBuf d_ritems, d_rstatus;
+  while (first || !items.empty() || !wide_items.empty()) {
+    if (!first && items.empty()) {  // narrow rounds are done: re-run the items whose u16 counters wrapped with u32 counters
       items.swap(wide_items);
       wide = true;
     }
     if (++round > 64) return fail(h, KC_ERR_CUDA, "count stage does not converge");
-    // Items are dealt round-robin to the CTAs. Hash partitions are statistically alike, so a full sort (6 ms for 10^5 items)
-    // buys nothing; only the outliers (skewed data: heavy-hitter partitions) are moved to the front, heaviest first, so that
-    // none of them starts last and becomes the tail.
-    if (items.size() <= 4096) {
-      std::stable_sort(items.begin(), items.end(), [](const WorkItem &a, const WorkItem &b) { return a.nsup > b.nsup; });
-    } else {
-      u64 sum = 0;
-      for (auto &it : items) sum += it.nsup;
-      const u64 thr = 2 * (sum / items.size()) + 1;
-      auto mid = std::stable_partition(items.begin(), items.end(), [thr](const WorkItem &a) { return a.nsup > thr; });
-      std::stable_sort(items.begin(), mid, [](const WorkItem &a, const WorkItem &b) { return a.nsup > b.nsup; });
-    }
-    ht.lap("finish: sort items");
     u32 tab_size, key_cap;
     table_geometry(h, wide, any_ctg, tab_size, key_cap);
     const int VW = (wide ? VR_WIDE : VR_NARROW) + (any_ctg ? V_CTG : 0);
     const size_t smem = count_smem_bytes(KW, VW, tab_size, key_cap) + 8;
-    RC(ensure(h, d_items, items.size() * sizeof(WorkItem)));
-    RC(ensure(h, d_status, items.size() * sizeof(ItemStatus)));
-    CK(cudaMemcpyAsync(d_items.p, items.data(), items.size() * sizeof(WorkItem), cudaMemcpyHostToDevice, h->s_main));
-    ca.items = (const WorkItem *)d_items.p;
-    ca.status = (ItemStatus *)d_status.p;
-    ca.nitems = (u32)items.size();
+    size_t nitems;
+    if (first) {
+      ca.items = (const WorkItem *)d_items.p;
+      ca.status = (ItemStatus *)d_status.p;
+      ca.heavy = (const u64 *)d_heavy.p;
+      ca.n_heavy = n_heavy;
+      nitems = nblk ? P : 0;
+    } else {
+      std::stable_sort(items.begin(), items.end(), [](const WorkItem &x, const WorkItem &y) { return x.nsup > y.nsup; });
+      nitems = items.size();
+      RC(ensure(h, d_ritems, nitems * sizeof(WorkItem)));
+      RC(ensure(h, d_rstatus, nitems * sizeof(ItemStatus)));
+      CK(cudaMemcpyAsync(d_ritems.p, items.data(), nitems * sizeof(WorkItem), cudaMemcpyHostToDevice, h->s_main));
+      ca.items = (const WorkItem *)d_ritems.p;
+      ca.status = (ItemStatus *)d_rstatus.p;
+      ca.heavy = nullptr;
+      ca.n_heavy = 0;
+    }
+    ca.nitems = (u32)nitems;
     ca.tab_size = tab_size;
     ca.key_cap = key_cap;
-    const unsigned grid = (unsigned)std::min<size_t>(items.size(), (size_t)h->sms);
-    ht.lap("finish: item upload");
-    CK(cudaEventRecord(h->ev_c, h->s_main));
-    RC(dispatch_count(h, wide, any_ctg, ca, smem, grid));
-    CK(cudaEventRecord(h->ev_d, h->s_main));
-    h->st.gpu_launches++;
-    h->st.n_insert_launches++;
-    status.resize(items.size());
-    CK(cudaMemcpyAsync(status.data(), d_status.p, items.size() * sizeof(ItemStatus), cudaMemcpyDeviceToHost, h->s_main));
+    if (nitems) {
+      const unsigned grid = (unsigned)std::min<size_t>(nitems, (size_t)h->sms);
+      CK(cudaEventRecord(h->ev_c, h->s_main));
+      RC(dispatch_count(h, wide, any_ctg, ca, smem, grid));
+      CK(cudaEventRecord(h->ev_d, h->s_main));
+      h->st.gpu_launches++;
+      h->st.n_insert_launches++;
+    }
+    CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
     CK(cudaStreamSynchronize(h->s_main));
-    ht.lap("finish: kernel + status D2H");
-    h->st.ms_insert += elapsed(h->ev_c, h->ev_d);
+    ht.lap("finish: count kernel");
+    if (nitems) h->st.ms_insert += elapsed(h->ev_c, h->ev_d);
     h->st.table_bytes_max = std::max<u64>(h->st.table_bytes_max, smem);
     std::vector<WorkItem> again;
-    for (size_t i = 0; i < items.size(); i++) {
-      const WorkItem &it = items[i];
-      if (status[i].overflow) {
-        // it filled its key store after `progress` of `nsup` supermers: split its hash range so that each child should end
-        // up around 60 % full
-        const double frac_done = std::max(1.0, (double)status[i].progress) / (double)it.nsup;
-        u32 f = 2;
-        while (f < 256 && (double)f * frac_done < 1.6) f <<= 1;
-        if ((u64)it.nsub * f > (1u << 20)) return fail(h, KC_ERR_CUDA, "partition %u cannot be split further", it.part);
-        for (u32 c = 0; c < f; c++) {
-          WorkItem ch = it;
-          ch.sub = it.sub + c * it.nsub;
-          ch.nsub = it.nsub * f;
-          again.push_back(ch);
+    if (ctr[CTR_RETRY] != retries_seen) {
+      retries_seen = ctr[CTR_RETRY];
+      if (first) {
+        items.resize(nitems);
+        CK(cudaMemcpy(items.data(), d_items.p, nitems * sizeof(WorkItem), cudaMemcpyDeviceToHost));
+      }
+      status.resize(nitems);
+      CK(cudaMemcpy(status.data(), ca.status, nitems * sizeof(ItemStatus), cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < nitems; i++) {
+        WorkItem it = items[i];
+        it.heavy = 0;
+        if (status[i].overflow) {
+          // it filled its key store after `progress` of `nsup` supermers: split its hash range so that each child should
+          // end up around 60 % full
+          const double frac_done = std::max(1.0, (double)status[i].progress) / (double)it.nsup;
+          u32 f = 2;
+          while (f < 256 && (double)f * frac_done < 1.6) f <<= 1;
+          if ((u64)it.nsub * f > (1u << 20)) return fail(h, KC_ERR_CUDA, "partition %u cannot be split further", it.part);
+          for (u32 c = 0; c < f; c++) {
+            WorkItem ch = it;
+            ch.sub = it.sub + c * it.nsub;
+            ch.nsub = it.nsub * f;
+            again.push_back(ch);
+          }
+          h->st.table_retries++;
+        } else if (status[i].wide) {
+          wide_items.push_back(it);
+          h->st.table_retries++;
         }
-        h->st.table_retries++;
-      } else if (status[i].wide) {
-        wide_items.push_back(it);
-        h->st.table_retries++;
       }
     }
     items.swap(again);
+    first = false;
   }
   CK(cudaEventRecord(e1, h->s_main));
-  u64 counters[8];
-  CK(cudaMemcpyAsync(counters, d_counters.p, 64, cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
   h->st.ms_finish += elapsed(e0, e1);
-  release(d_counters);
-  release(d_segs);
-  release(d_items);
-  release(d_status);
-  if (counters[3]) return fail(h, KC_ERR_OVERFLOW, "survivor output capacity exceeded");
-  h->n_surv = counters[0];
-  h->n_pf = counters[1];
-  h->st.distinct = counters[2];
-  h->st.survivors = counters[0];
-  h->st.purged = counters[2] - counters[0];
-  h->st.max_probe = counters[4];
+  for (DevBuf *b : {&d_counters, &d_segs, &d_items, &d_status, &d_descs, &d_heavy, &d_ritems, &d_rstatus}) release(*b);
+  if (ctr[CTR_ERR]) return fail(h, KC_ERR_OVERFLOW, "survivor output capacity exceeded");
+  h->n_surv = ctr[CTR_SURV];
+  h->n_pf = ctr[CTR_PF];
+  h->st.distinct = ctr[CTR_DISTINCT];
+  h->st.survivors = ctr[CTR_SURV];
+  h->st.purged = ctr[CTR_DISTINCT] - ctr[CTR_SURV];
+  h->st.max_probe = ctr[CTR_MAXPROBE];
   u64 inst_parsed = 0;
   CK(cudaMemcpy(&inst_parsed, h->d_misc.p, 8, cudaMemcpyDeviceToHost));
   h->st.instances_parsed = inst_parsed;
   // supermer buffers are no longer needed (KmerDHT::clear_stores, kmer_dht.cpp:156-159)
-  for (auto &b : h->blocks) dev_free(b.rec);
-  for (auto &b : h->rblocks) dev_free(b.rec);
+  for (auto &b : h->blocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
+  for (auto &b : h->rblocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   h->blocks.clear();
   h->rblocks.clear();
   h->finished = true;
@@ -946,10 +1032,11 @@ extern "C" int kc_destroy(kc_handle *h) {
   cudaSetDevice(h->cfg.device);
   if (h->s_main) cudaStreamSynchronize(h->s_main);
   if (h->s_copy) cudaStreamSynchronize(h->s_copy);
-  for (auto &b : h->blocks) dev_free(b.rec);
-  for (auto &b : h->rblocks) dev_free(b.rec);
-  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_hist, &h->d_cursor,
-                    &h->d_base, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
+  if (h->s_comm) cudaStreamSynchronize(h->s_comm);
+  for (auto &b : h->blocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
+  for (auto &b : h->rblocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
+  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_cursor, &h->d_meta, &h->d_meta_all,
+                    &h->d_tot, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
                     &h->pf_keys, &h->pf_vals};
   for (DevBuf *b : bufs) release(*b);
   if (h->ev_a) cudaEventDestroy(h->ev_a);
@@ -962,6 +1049,12 @@ extern "C" int kc_destroy(kc_handle *h) {
   }
   if (h->s_main) cudaStreamDestroy(h->s_main);
   if (h->s_copy) cudaStreamDestroy(h->s_copy);
+  if (h->s_comm) cudaStreamDestroy(h->s_comm);
+  pin_put(h->h_pin, h->pin_bytes);
+  for (auto &p : h->pending) { dev_free(p.dir); dev_free(p.rec); }
+  if (h->ev_fill) cudaEventDestroy(h->ev_fill);
+  if (h->ev_x0) cudaEventDestroy(h->ev_x0);
+  if (h->ev_x1) cudaEventDestroy(h->ev_x1);
   void kc_comm_destroy(kc_handle *);
   kc_comm_destroy(h);
   delete h;

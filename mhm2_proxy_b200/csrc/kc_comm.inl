@@ -20,22 +20,19 @@
 
 namespace {
 
-// a received run: directory (P entries) already on the host, hdr/payload device buffers owned by the block
-int make_rblock(kc_handle *h, const BucketHist *dir, u32 *rec, bool is_ctg) {
-  const u32 P = h->P;
+// a received run: directory (P entries) and records are device buffers now owned by the block; its bucket layout is
+// computed on `st` (the stream the data arrived on)
+int make_rblock(kc_handle *h, BucketHist *dir, u32 *rec, u64 nsup, bool is_ctg, cudaStream_t st) {
   Block b;
   b.received = true;
   b.is_ctg = is_ctg;
   b.rec = rec;
-  b.hist.assign(dir, dir + P);
-  b.rec_base.resize(P + 1);
-  u64 hs = 0;
-  for (u32 p = 0; p < P; p++) {
-    b.rec_base[p] = hs;
-    hs += dir[p].nsup;
-  }
-  b.rec_base[P] = hs;
-  b.tot_sup = hs;
+  b.d_hist = dir;
+  b.tot_sup = nsup;
+  CK(dev_alloc((void **)&b.d_base, sizeof(u64) * h->P));
+  bucket_scan_kernel<<<1, 1024, 0, st>>>(dir, h->P, b.d_base, h->P, nullptr);
+  h->st.gpu_launches++;
+  CK(cudaGetLastError());
   h->rblocks.push_back(std::move(b));
   return KC_OK;
 }
@@ -148,108 +145,132 @@ extern "C" int kc_comm_init(kc_handle *h, const uint8_t id128[128]) {
 
 void kc_comm_destroy(kc_handle *h) { h->comm = nullptr; /* cached communicators live until process exit */ }
 
-// NCCL transport. Collective: every shard calls it once, from kc_finish.
-int kc_exchange(kc_handle *h) {
+namespace {
+
+// round metadata travels to the device as kernel parameters: a host-to-device copy would queue behind the bulk copy of
+// the next batch of reads on the copy engine
+constexpr int META_INLINE = 96;
+struct MetaWords {
+  u64 v[META_INLINE];
+};
+__global__ void meta_store_kernel(const MetaWords m, int n, u64 *dst) {
+  if ((int)threadIdx.x < n) dst[threadIdx.x] = m.v[threadIdx.x];
+}
+
+// One exchange round over NCCL. Collective, but NOT tied to a batch number: a shard calls it whenever it has a parsed
+// block to hand out (blk != null, from parse_batch right after FILL was launched) and, from kc_finish, with blk == null and
+// done == true until every shard has said "done" in the same round. Round r of one shard pairs with round r of every
+// other shard, whatever each of them brought. Per round:
+//   1. all-gather of [done, is_ctg, P, nsup for each destination] (N+3 words per shard),
+//   2. one NCCL group on the comm stream: my directory slice (P entries) + my record range to every destination that gets
+//      something, and the matching receives. Between a pair of ranks the order is (directory, records).
+// The group is not waited for: it runs on s_comm behind the "FILL done" event while the main stream parses the next batch;
+// receives are turned into blocks in finish_exchange.
+int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
 #if KC_HAVE_NCCL_H
-  if (!h->comm) return fail(h, KC_ERR_COMM, "multi-shard handle without a communicator: call kc_comm_init first");
   NcclApi &a = nccl_api();
   const int N = h->cfg.num_shards, me = h->cfg.shard_id;
-  const u32 P = h->P;
-  cudaStream_t st = h->s_main;
-  cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
-  CK(cudaEventRecord(e0, st));
-  // 1. agree on (P, number of blocks) ...
-  DevBuf d_meta, d_all;
-  u64 mine[2] = {P, (u64)h->blocks.size()};
-  RC(ensure(h, d_meta, 16));
-  RC(ensure(h, d_all, 16 * (size_t)N));
-  CK(cudaMemcpyAsync(d_meta.p, mine, 16, cudaMemcpyHostToDevice, st));
-  NC(a.AllGather(d_meta.p, d_all.p, 2, ncclUint64, h->comm->comm, st));
-  std::vector<u64> all(2 * (size_t)N);
-  CK(cudaMemcpyAsync(all.data(), d_all.p, 16 * (size_t)N, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  u64 maxb = 0;
-  for (int r = 0; r < N; r++) {
-    if (all[2 * r] != P)
-      return fail(h, KC_ERR_INVALID, "shards disagree on num_partitions (%llu vs %u): set cfg.num_partitions or expected_instances",
-                  (unsigned long long)all[2 * r], P);
-    maxb = std::max(maxb, all[2 * r + 1]);
-  }
-  if (maxb == 0) return KC_OK;
-  // 2. ... then on every (block, destination) size: per block [is_ctg, nsup x N]
-  const size_t rec = 1 + (size_t)N, per_rank = maxb * rec;
+  const size_t MW = (size_t)N + 3;
   const size_t RB = (size_t)h->geom.rw * 4;  // bytes per supermer record
-  std::vector<u64> sz(per_rank, 0), szall(per_rank * N);
-  for (size_t b = 0; b < h->blocks.size(); b++) {
-    const Block &blk = h->blocks[b];
-    sz[b * rec] = blk.is_ctg ? 1 : 0;
-    for (int d = 0; d < N; d++) {
-      sz[b * rec + 1 + d] = blk.tot_sup ? blk.rec_base[(size_t)(d + 1) * P] - blk.rec_base[(size_t)d * P] : 0;
-    }
+  cudaStream_t st = h->s_comm;
+  RC(ensure(h, h->d_meta, MW * 8));
+  RC(ensure(h, h->d_meta_all, MW * 8 * N));
+  std::vector<u64> mine(MW, 0);
+  mine[0] = done ? 1 : 0;
+  mine[1] = blk && blk->is_ctg ? 1 : 0;
+  mine[2] = h->P;
+  if (blk && blk->tot_sup)
+    for (int d = 0; d < N; d++)
+      if (d != me) mine[3 + d] = blk->dest_base[d + 1] - blk->dest_base[d];
+  if (MW <= (size_t)META_INLINE) {
+    MetaWords mw;
+    memcpy(mw.v, mine.data(), MW * 8);
+    meta_store_kernel<<<1, META_INLINE, 0, st>>>(mw, (int)MW, (u64 *)h->d_meta.p);
+    h->st.gpu_launches++;
+    CK(cudaGetLastError());
+  } else {
+    CK(cudaMemcpyAsync(h->d_meta.p, mine.data(), MW * 8, cudaMemcpyHostToDevice, st));
   }
-  RC(ensure(h, d_meta, per_rank * 8));
-  RC(ensure(h, d_all, per_rank * 8 * N));
-  CK(cudaMemcpyAsync(d_meta.p, sz.data(), per_rank * 8, cudaMemcpyHostToDevice, st));
-  NC(a.AllGather(d_meta.p, d_all.p, per_rank, ncclUint64, h->comm->comm, st));
-  CK(cudaMemcpyAsync(szall.data(), d_all.p, per_rank * 8 * N, cudaMemcpyDeviceToHost, st));
+  NC(a.AllGather(h->d_meta.p, h->d_meta_all.p, MW, ncclUint64, h->comm->comm, st));
+  u64 *h_all = h->h_pin + PIN_META / 8;
+  CK(cudaMemcpyAsync(h_all, h->d_meta_all.p, MW * 8 * N, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  // 3. directories of my blocks on the device (P entries per destination are sent along)
-  std::vector<BucketHist *> d_dirs(h->blocks.size(), nullptr);
-  for (size_t b = 0; b < h->blocks.size(); b++) {
-    if (!h->blocks[b].tot_sup) continue;
-    CK(dev_alloc((void **)&d_dirs[b], sizeof(BucketHist) * (size_t)N * P));
-    CK(cudaMemcpyAsync(d_dirs[b], h->blocks[b].hist.data(), sizeof(BucketHist) * (size_t)N * P, cudaMemcpyHostToDevice, st));
+  const u64 *all = h_all;
+  bool everyone = true;
+  u64 P = h->P;
+  for (int r = 0; r < N; r++) {
+    everyone = everyone && all[r * MW] != 0;
+    const u64 pr = all[r * MW + 2];
+    if (pr && !P) P = pr;
+    if (pr && pr != P)
+      return fail(h, KC_ERR_INVALID, "shards disagree on num_partitions (%llu vs %llu): set cfg.num_partitions or expected_instances",
+                  (unsigned long long)pr, (unsigned long long)P);
   }
-  // 4. receive buffers
-  struct Incoming { BucketHist *dir; u32 *rec; u64 nsup; bool ctg; int src; };
-  std::vector<Incoming> inc;
+  if (all_done) *all_done = everyone;
+  if (!h->P && P) {  // this shard had nothing to parse so far: take the peers' geometry
+    h->P = (u32)P;
+    h->st.num_partitions = h->P;
+  }
+  // receive buffers
+  struct In { Pending p; int src; };
+  std::vector<In> inc;
   for (int s = 0; s < N; s++) {
     if (s == me) continue;
-    for (u64 b = 0; b < all[2 * s + 1]; b++) {
-      const u64 *r = &szall[(size_t)s * per_rank + b * rec];
-      const u64 nsup = r[1 + me];
-      if (!nsup) continue;
-      Incoming in{nullptr, nullptr, nsup, r[0] != 0, s};
-      CK(dev_alloc((void **)&in.dir, sizeof(BucketHist) * P));
-      CK(dev_alloc((void **)&in.rec, RB * nsup + 64));
-      inc.push_back(in);
-    }
+    const u64 nsup = all[s * MW + 3 + me];
+    if (!nsup) continue;
+    In in;
+    in.src = s;
+    in.p.nsup = nsup;
+    in.p.is_ctg = all[s * MW + 1] != 0;
+    CK(dev_alloc((void **)&in.p.dir, sizeof(BucketHist) * P));
+    CK(dev_alloc((void **)&in.p.rec, RB * nsup + 64));
+    inc.push_back(in);
   }
-  // 5. one group: all sends and receives; between a pair of ranks the order is (block asc; dir, hdr, payload)
+  bool any_send = false;
+  for (int d = 0; d < N; d++) any_send = any_send || mine[3 + d] != 0;
+  if (inc.empty() && !any_send) return KC_OK;
+  if (any_send) CK(cudaStreamWaitEvent(st, h->ev_fill, 0));  // the records are being written by FILL on the main stream
   NC(a.GroupStart());
   u64 sent = 0;
   for (int d = 0; d < N; d++) {
-    if (d == me) continue;
-    for (size_t b = 0; b < h->blocks.size(); b++) {
-      const Block &blk = h->blocks[b];
-      const u64 nsup = sz[b * rec + 1 + d];
-      if (!nsup) continue;
-      NC(a.Send(d_dirs[b] + (size_t)d * P, sizeof(BucketHist) * P, ncclUint8, d, h->comm->comm, st));
-      NC(a.Send(blk.rec + blk.rec_base[(size_t)d * P] * h->geom.rw, RB * nsup, ncclUint8, d, h->comm->comm, st));
-      sent += sizeof(BucketHist) * P + RB * nsup;
-    }
+    const u64 nsup = mine[3 + d];
+    if (!nsup) continue;
+    NC(a.Send(blk->d_hist + (size_t)d * P, sizeof(BucketHist) * P, ncclUint8, d, h->comm->comm, st));
+    NC(a.Send(blk->rec + blk->dest_base[d] * h->geom.rw, RB * nsup, ncclUint8, d, h->comm->comm, st));
+    sent += sizeof(BucketHist) * P + RB * nsup;
   }
   for (auto &in : inc) {
-    NC(a.Recv(in.dir, sizeof(BucketHist) * P, ncclUint8, in.src, h->comm->comm, st));
-    NC(a.Recv(in.rec, RB * in.nsup, ncclUint8, in.src, h->comm->comm, st));
+    NC(a.Recv(in.p.dir, sizeof(BucketHist) * P, ncclUint8, in.src, h->comm->comm, st));
+    NC(a.Recv(in.p.rec, RB * in.p.nsup, ncclUint8, in.src, h->comm->comm, st));
   }
   NC(a.GroupEnd());
-  // 6. directories back to the host -> rblocks
-  std::vector<BucketHist> dirs(inc.size() * (size_t)P);
-  for (size_t i = 0; i < inc.size(); i++)
-    CK(cudaMemcpyAsync(&dirs[i * P], inc[i].dir, sizeof(BucketHist) * P, cudaMemcpyDeviceToHost, st));
-  CK(cudaEventRecord(e1, st));
-  CK(cudaStreamSynchronize(st));
-  for (size_t i = 0; i < inc.size(); i++) {
-    make_rblock(h, &dirs[i * P], inc[i].rec, inc[i].ctg);
-    dev_free(inc[i].dir);
-  }
-  for (auto p : d_dirs)
-    if (p) dev_free(p);
-  release(d_meta);
-  release(d_all);
-  h->st.ms_exchange += elapsed(e0, e1);
+  for (auto &in : inc) h->pending.push_back(in.p);
   h->st.supermer_bytes_sent += sent;
+  return KC_OK;
+#else
+  (void)blk; (void)done; (void)all_done;
+  return fail(h, KC_ERR_COMM, "built without nccl.h");
+#endif
+}
+
+}  // namespace
+
+// NCCL transport, the part that runs in kc_finish: empty rounds until every shard is done, then the receives become blocks.
+// ms_exchange is the exchange time the count phase actually waits for (what the per-batch rounds did not hide).
+int kc_exchange(kc_handle *h) {
+#if KC_HAVE_NCCL_H
+  if (!h->comm) return fail(h, KC_ERR_COMM, "multi-shard handle without a communicator: call kc_comm_init first");
+  CK(cudaEventRecord(h->ev_x0, h->s_main));  // the main stream is idle here: x0..x1 is what kc_finish waits for
+  for (bool all_done = false; !all_done;) RC(exchange_round(h, nullptr, true, &all_done));
+  if (!h->P) decide_partitions(h, 0);
+  for (auto &pd : h->pending) RC(make_rblock(h, pd.dir, pd.rec, pd.nsup, pd.is_ctg, h->s_comm));
+  h->pending.clear();
+  CK(cudaEventRecord(h->ev_fill, h->s_comm));
+  CK(cudaStreamWaitEvent(h->s_main, h->ev_fill, 0));
+  CK(cudaEventRecord(h->ev_x1, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
+  CK(cudaStreamSynchronize(h->s_comm));
+  h->st.ms_exchange += elapsed(h->ev_x0, h->ev_x1);
   return KC_OK;
 #else
   return fail(h, KC_ERR_COMM, "built without nccl.h");
@@ -278,15 +299,19 @@ extern "C" int kc_finish_local_group(kc_handle **hs, int32_t n) {
       if (!blk.tot_sup) continue;
       for (int d = 0; d < n; d++) {
         if (d == s) continue;
-        const u64 nsup = blk.rec_base[(size_t)(d + 1) * P] - blk.rec_base[(size_t)d * P];
+        const u64 nsup = blk.dest_base[d + 1] - blk.dest_base[d];
         if (!nsup) continue;
         kc_handle *hd = hs[d];
         const size_t RB = (size_t)h->geom.rw * 4;
         u32 *rec = nullptr;
+        BucketHist *dir = nullptr;
         CK(cudaSetDevice(hd->cfg.device));
         CK(dev_alloc((void **)&rec, RB * nsup + 64));
-        CK(cudaMemcpyPeer(rec, hd->cfg.device, blk.rec + blk.rec_base[(size_t)d * P] * h->geom.rw, h->cfg.device, RB * nsup));
-        make_rblock(hd, &blk.hist[(size_t)d * P], rec, blk.is_ctg);
+        CK(dev_alloc((void **)&dir, sizeof(BucketHist) * P));
+        // the source was synchronised above; everything on the destination side is ordered on its main stream
+        CK(cudaMemcpyPeerAsync(rec, hd->cfg.device, blk.rec + blk.dest_base[d] * h->geom.rw, h->cfg.device, RB * nsup, hd->s_main));
+        CK(cudaMemcpyPeerAsync(dir, hd->cfg.device, blk.d_hist + (size_t)d * P, h->cfg.device, sizeof(BucketHist) * P, hd->s_main));
+        RC(make_rblock(hd, dir, rec, nsup, blk.is_ctg, hd->s_main));
         h->st.supermer_bytes_sent += RB * nsup;
       }
     }

@@ -53,8 +53,21 @@ struct WorkItem {
   u32 nsup;                // supermers of the partition
   u32 part;
   u32 sub, nsub;           // this item takes k-mers with ((hash >> 40) & (nsub - 1)) == sub; nsub is a power of two
-  u32 pad[2];
+  u32 heavy;               // far above the mean: scheduled through CountArgs::heavy ahead of everything else
+  u32 pad;
 };
+
+struct BlockDesc {  // one parsed or received batch as the item builder sees it (all pointers are device memory)
+  const u32 *rec;
+  const BucketHist *hist;  // per bucket
+  const u64 *base;         // exclusive scan of hist[].nsup
+  u32 first;               // bucket of this shard's partition 0 inside hist/base
+  u32 is_ctg;
+};
+
+// counters[] slots shared by the item builder, the count kernel and the host
+enum { CTR_SURV = 0, CTR_PF = 1, CTR_DISTINCT = 2, CTR_ERR = 3, CTR_MAXPROBE = 4, CTR_RETRY = 5, CTR_READ_INST = 6, CTR_CTG_INST = 7,
+       CTR_NHEAVY = 8, CTR_SUP = 9, CTR_WORDS = 16 };
 
 struct ItemStatus {
   u32 overflow;  // ran out of key slots: emitted nothing, must be re-run with more sub-passes
@@ -67,7 +80,8 @@ struct CountArgs {
   const WorkItem *items;
   const SegDesc *segs;
   ItemStatus *status;
-  u32 nitems;
+  const u64 *heavy;  // [n_heavy] (nsup << 32 | item index), heaviest first
+  u32 nitems, n_heavy;
   int k;
   int rw, nwb;     // record geometry (kc_parse.cuh)
   u32 tab_size, key_cap;  // tab_size u32 entries (multiple of 4)
@@ -77,7 +91,7 @@ struct CountArgs {
   uint16_t *out_counts;
   char *out_left, *out_right;
   u64 out_cap;
-  u64 *counters;   // [0] survivors cursor, [1] prefilter cursor, [2] distinct, [3] output overflow flag, [4] max probe
+  u64 *counters;   // CTR_* slots
   u64 *pf_keys;    // optional pre-filter dump (reads-pass counters), may be null
   uint16_t *pf_vals;
   u64 pf_cap;
@@ -123,7 +137,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   SegDesc *segc = (SegDesc *)(vals + (size_t)a.key_cap * VW + ((a.key_cap * VW) & 1));  // [SEG_CACHE], 8-byte aligned
   __shared__ u64 s_obase[2];
   __shared__ __align__(16) WorkItem s_work;
-  __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed;
+  __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed, s_widx;
   __shared__ u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];
   __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -136,25 +150,43 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const u32 nbuckets = a.tab_size >> 2;
   const int sup_per_chunk = min(GRP_THREADS, GRP_STAGE_WORDS / rw);
   u32 my_max_probe = 0;
-  // Work items are sorted heaviest first and dealt round-robin to the CTAs; the next item's descriptor is fetched while
-  // the current one is being processed.
+  // Work items are dealt round-robin to the CTAs: first the heavy list (outlier partitions, heaviest first, so that none of
+  // them starts last and becomes the tail), then every item in partition order, skipping the ones the heavy list covered.
+  // The next item's descriptor is fetched while the current one is being processed.
+  const u32 nvirt = a.n_heavy + a.nitems;
   if (tid == 0) {
     s_prev = a.key_cap;  // shared memory starts undefined: the first item clears every counter
-    if (blockIdx.x < a.nitems) s_work = a.items[blockIdx.x];
+    if (blockIdx.x < nvirt) {
+      const u32 i0 = blockIdx.x < a.n_heavy ? (u32)a.heavy[blockIdx.x] : blockIdx.x - a.n_heavy;
+      s_work = a.items[i0];
+      s_widx = i0;
+    }
   }
 
-  for (u32 item_idx = blockIdx.x; item_idx < a.nitems; item_idx += gridDim.x) {
+  for (u32 virt = blockIdx.x; virt < nvirt; virt += gridDim.x) {
     __syncthreads();
     const u32 prev = s_prev;
     const WorkItem it = s_work;
-    const bool have_nx = tid == 0 && item_idx + gridDim.x < a.nitems;
+    const u32 item_idx = s_widx;
+    const bool have_nx = tid == 0 && virt + gridDim.x < nvirt;
     uint4 nx0 = make_uint4(0, 0, 0, 0), nx1 = nx0;
+    u32 nx_idx = 0;
     if (have_nx) {
-      const uint4 *pn = (const uint4 *)(a.items + item_idx + gridDim.x);
+      const u32 nv = virt + gridDim.x;
+      nx_idx = nv < a.n_heavy ? (u32)__ldg(a.heavy + nv) : nv - a.n_heavy;
+      const uint4 *pn = (const uint4 *)(a.items + nx_idx);
       nx0 = __ldg(pn);
       nx1 = __ldg(pn + 1);
     }
     __syncthreads();
+    if (it.nsup == 0 || (it.heavy && virt >= a.n_heavy)) {  // empty partition, or already done through the heavy list
+      if (have_nx) {
+        ((uint4 *)&s_work)[0] = nx0;
+        ((uint4 *)&s_work)[1] = nx1;
+        s_widx = nx_idx;
+      }
+      continue;
+    }
     if (tid == 0) {
       s_nkeys = 0;
       s_over = 0;
@@ -346,7 +378,9 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       if (have_nx) {
         ((uint4 *)&s_work)[0] = nx0;
         ((uint4 *)&s_work)[1] = nx1;
+        s_widx = nx_idx;
       }
+      if (over || wide_needed) atomicAdd((unsigned long long *)&a.counters[CTR_RETRY], 1ull);
     }
     if (over || wide_needed) continue;
 
@@ -425,8 +459,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         warp_p[lane] = ip - p;
         const u32 totc = __shfl_sync(0xffffffffu, ic, 31), totp = __shfl_sync(0xffffffffu, ip, 31);
         if (lane == 0) {
-          s_obase[0] = totc ? atomicAdd(&a.counters[0], (u64)totc) : 0ull;
-          s_obase[1] = totp ? atomicAdd(&a.counters[1], (u64)totp) : 0ull;
+          s_obase[0] = totc ? atomicAdd(&a.counters[CTR_SURV], (u64)totc) : 0ull;
+          s_obase[1] = totp ? atomicAdd(&a.counters[CTR_PF], (u64)totp) : 0ull;
         }
       }
       __syncthreads();
@@ -439,7 +473,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           a.out_left[o] = le;
           a.out_right[o] = re;
         } else {
-          a.counters[3] = 1;
+          a.counters[CTR_ERR] = 1;
         }
       }
       if (pf) {
@@ -459,15 +493,80 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             ov[5] = (uint16_t)(w2 >> 16); ov[6] = (uint16_t)w3; ov[7] = (uint16_t)(w3 >> 16); ov[8] = (uint16_t)w4;
           }
         } else {
-          a.counters[3] = 1;
+          a.counters[CTR_ERR] = 1;
         }
       }
     }
     __syncthreads();
-    if (tid == 0 && s_live) atomicAdd(&a.counters[2], (u64)s_live);
+    if (tid == 0 && s_live) atomicAdd(&a.counters[CTR_DISTINCT], (u64)s_live);
   }
   my_max_probe = __reduce_max_sync(0xffffffffu, my_max_probe);
-  if (lane == 0 && my_max_probe) atomicMax(&a.counters[4], (u64)my_max_probe);
+  if (lane == 0 && my_max_probe) atomicMax(&a.counters[CTR_MAXPROBE], (u64)my_max_probe);
+}
+
+// Work items of the count stage, built where the bucket directories already are. One thread per partition of this shard:
+// its runs of supermers in every parsed / received batch become the segment list of one item (a fixed slot of nblk
+// descriptors per partition, so no compaction and no host involvement); partitions far above the mean are also appended to
+// the heavy list. Totals (instances from reads / contigs, supermers) are reduced into counters[].
+struct BuildArgs {
+  const BlockDesc *blocks;
+  u32 nblk, P;
+  int rw;
+  u64 heavy_thr;  // nsup above this -> heavy
+  SegDesc *segs;  // [P * nblk]
+  WorkItem *items;  // [P]
+  u64 *heavy;     // [P]
+  u64 *counters;
+};
+
+__global__ void __launch_bounds__(256) build_items_kernel(const BuildArgs a) {
+  const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+  u64 nsup = 0, ri = 0, ci = 0;
+  if (p < a.P) {
+    const u32 s0 = p * a.nblk;
+    u32 cnt = 0;
+    for (u32 j = 0; j < a.nblk; j++) {
+      const BlockDesc d = a.blocks[j];
+      const u32 bu = d.first + p;
+      const BucketHist hh = d.hist[bu];
+      if (!hh.nsup) continue;
+      SegDesc sd;
+      sd.rec = d.rec + (size_t)d.base[bu] * a.rw;
+      sd.nsup = hh.nsup;
+      sd.is_ctg = d.is_ctg;
+      sd.sup0 = (u32)nsup;
+      sd.pad = 0;
+      a.segs[s0 + cnt++] = sd;
+      nsup += hh.nsup;
+      if (d.is_ctg) ci += hh.ninst; else ri += hh.ninst;
+    }
+    WorkItem it;
+    it.seg_begin = s0;
+    it.seg_end = s0 + cnt;
+    it.nsup = (u32)nsup;
+    it.part = p;
+    it.sub = 0;
+    it.nsub = 1;
+    it.heavy = nsup > a.heavy_thr ? 1u : 0u;
+    it.pad = 0;
+    a.items[p] = it;
+    if (nsup > 0xFFFFFFF0ull) a.counters[CTR_ERR] = 2;  // a partition this large cannot be indexed: more partitions needed
+    if (it.heavy) {
+      const u64 slot = atomicAdd((unsigned long long *)&a.counters[CTR_NHEAVY], 1ull);
+      a.heavy[slot] = (nsup << 32) | p;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) {
+    nsup += __shfl_xor_sync(0xffffffffu, nsup, d);
+    ri += __shfl_xor_sync(0xffffffffu, ri, d);
+    ci += __shfl_xor_sync(0xffffffffu, ci, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (nsup) atomicAdd((unsigned long long *)&a.counters[CTR_SUP], (unsigned long long)nsup);
+    if (ri) atomicAdd((unsigned long long *)&a.counters[CTR_READ_INST], (unsigned long long)ri);
+    if (ci) atomicAdd((unsigned long long *)&a.counters[CTR_CTG_INST], (unsigned long long)ci);
+  }
 }
 
 }  // namespace kc

@@ -41,6 +41,27 @@ def main():
             print(f"rank {rank} k={k}: {len(keys)} survivors (oracle {int(sel.sum())}), sent {st['supermer_bytes_sent']} B, "
                   f"exchange {st['ms_exchange']:.2f} ms, ok={good}", flush=True)
             ok = ok and good
+    # ragged case: unequal numbers of batches per rank, the last rank has nothing to parse and learns the partition count
+    # from its peers during the exchange rounds
+    k = 33
+    rb, ro = synth.make_reads(7000, com, error_rate=0.01, seed=77, n_rate=1e-3)
+    ref = harness.run("port", k, rb, ro, num_shards=world)
+    n = len(ro) - 1
+    cuts = [0] + [int(n * (1 - 0.5 ** (r + 1))) for r in range(world - 1)] + [n]
+    cuts[-2] = n  # last rank: empty
+    r0, r1 = cuts[rank], cuts[rank + 1]
+    with kcount.KmerCounter(k, num_shards=world, shard_id=rank, device=local, expected_instances=4_000_000,
+                            batch_reads=1000) as kc:
+        kc.comm_init(uid)
+        if r1 > r0:
+            kc.add_reads(rb[int(ro[r0]):int(ro[r1])], ro[r0:r1 + 1] - ro[r0])
+        kc.finish()
+        keys, counts, left, right = kc.survivors()
+        sel = ref.shard == rank
+        good = (np.array_equal(keys, ref.keys[sel]) and np.array_equal(counts, ref.counts[sel])
+                and np.array_equal(left, ref.left[sel]) and np.array_equal(right, ref.right[sel]))
+        print(f"rank {rank} ragged k={k}: reads {r1 - r0}, {len(keys)} survivors (oracle {int(sel.sum())}), ok={good}", flush=True)
+        ok = ok and good
     t = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0 and int(t.item()) == 1:
