@@ -74,7 +74,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "25",
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -195,15 +195,15 @@ def one_pass(kcount, k, args, rank, world, dev, mode, tb, to, d_b, d_o, uid, hou
             kc.add_reads_device(d_b.data_ptr(), d_o.data_ptr(), n, d_b.numel(), READ_LEN)
         else:
             kc.add_reads_ptr(tb.data_ptr(), to.data_ptr(), n)
-        kc.finish()
         d2h = 0
         if mode == "host":
+            # the call a drop-in user makes: finish and receive the table in host memory (kc_finish_to_host)
             nl = k // 32 + 1
-            ns = kc.num_survivors()
-            if ns * nl > hout.keys.numel() or ns > hout.cap:
-                raise SystemExit(f"bench.py: host output buffers too small for {ns} survivors")
-            kc.survivors_into(hout.keys.data_ptr(), hout.counts.data_ptr(), hout.left.data_ptr(), hout.right.data_ptr())
+            cap = min(hout.cap, hout.keys.numel() // nl)
+            ns = kc.finish_into(hout.keys.data_ptr(), hout.counts.data_ptr(), hout.left.data_ptr(), hout.right.data_ptr(), cap)
             d2h = ns * (8 * nl + 4)
+        else:
+            kc.finish()
         st = kc.stats()
         st["d2h_bytes"] = d2h
         return st
@@ -300,6 +300,8 @@ def run_ours(args):
         alg_bytes += ik * b_alg(k)
         per_k[str(k)] = {"instances_per_pass": sk[0]["instances_parsed"], "distinct": sk[0]["distinct"], "survivors": sk[0]["survivors"],
                          "partitions": sk[0]["num_partitions"], "supermers": sk[0]["supermers_out"],
+                         "instances_counted_rank0": sk[0]["instances_inserted"], "supermers_counted_rank0": sk[0]["supermers_in"],
+                         "max_probe": sk[0]["max_probe"],
                          "supermer_bytes": sk[0]["supermer_bytes_out"], "table_retries": sk[0]["table_retries"],
                          "table_group_bytes_max": sk[0]["table_bytes_max"],
                          "ms": {kk: round(sum(s[kk] for s in sk) / len(sk), 3) for kk in

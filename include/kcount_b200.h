@@ -119,6 +119,13 @@ int kc_finish_local_group(kc_handle **handles, int32_t n);
 /* KmerDHT::flush_updates + finish_updates -> HashTableInserter::insert_into_local_hashtable
  * (kmer_dht.cpp:227-236, kcount_cpu.cpp:490-528). Collective across shards when num_shards > 1. */
 int kc_finish(kc_handle *h);
+/* kc_finish + kc_copy_survivors in one call, for callers that want the table on the host (insert_into_local_hashtable fills
+ * the host-side local_kmers, kcount_cpu.cpp:490-528): the count stage runs in slices and the survivors of one slice travel
+ * to the host arrays while the next slice is counted. capacity = entries the arrays can hold (kmer_words: capacity *
+ * N_LONGS); *n_out = survivors. More survivors than capacity -> KC_ERR_OVERFLOW with the first `capacity` entries delivered
+ * and the whole table still on the device (kc_num_survivors / kc_copy_survivors). Pinned host arrays overlap best. */
+int kc_finish_to_host(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char *left, char *right, uint64_t capacity,
+                      uint64_t *n_out);
 
 /* local_kmers of this shard (kmer_dht.hpp:119, dbjg_traversal.cpp:301): n rows of N_LONGS words, u16 count, left, right */
 int kc_num_survivors(kc_handle *h, uint64_t *n);

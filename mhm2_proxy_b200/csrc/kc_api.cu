@@ -68,6 +68,7 @@ struct kc_handle {
   u64 *h_pin = nullptr;  // pinned scratch (PIN_BYTES): [0, PIN_META) bucket totals / counters, [PIN_META, ..) exchange metadata
   size_t pin_bytes = 0;
   cudaEvent_t ev_fill = nullptr, ev_x0 = nullptr, ev_x1 = nullptr;
+  std::vector<cudaEvent_t> ev_chunk;  // kc_finish_to_host: one per slice of the count stage
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr, ev_copy[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
   std::vector<Block> blocks;       // produced locally
   std::vector<Block> rblocks;      // received from peers (multi-shard)
@@ -719,9 +720,44 @@ int dispatch_count(kc_handle *h, bool wide, bool ctg, const CountArgs &ca, size_
 }  // namespace
 
 int kc_exchange(kc_handle *h);  // kc_comm.inl
-int finish_count(kc_handle *h);
+// where the surviving table goes when the caller wants it on the host as it is produced (kc_finish_to_host)
+struct HostSink {
+  u64 *keys = nullptr;
+  uint16_t *counts = nullptr;
+  char *left = nullptr, *right = nullptr;
+  u64 cap = 0;     // entries the host arrays can take
+  u64 copied = 0;  // entries already on their way
+};
 
-extern "C" int kc_finish(kc_handle *h) {
+int finish_count(kc_handle *h, HostSink *sink = nullptr);
+
+namespace {
+int finish_impl(kc_handle *h, HostSink *sink);
+}
+
+extern "C" int kc_finish(kc_handle *h) { return finish_impl(h, nullptr); }
+
+extern "C" int kc_finish_to_host(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char *left, char *right, uint64_t capacity,
+                                 uint64_t *n_out) {
+  if (!h || !kmer_words || !counts || !left || !right || !n_out) return KC_ERR_INVALID;
+  HostSink sink;
+  sink.keys = (u64 *)kmer_words;
+  sink.counts = counts;
+  sink.left = left;
+  sink.right = right;
+  sink.cap = capacity;
+  *n_out = 0;
+  int rc = finish_impl(h, &sink);
+  if (rc) return rc;
+  *n_out = h->n_surv;
+  if (h->n_surv > capacity)
+    return fail(h, KC_ERR_OVERFLOW, "%llu survivors do not fit the host arrays (%llu): the table is still on the device, use "
+                "kc_copy_survivors", (unsigned long long)h->n_surv, (unsigned long long)capacity);
+  return KC_OK;
+}
+
+namespace {
+int finish_impl(kc_handle *h, HostSink *sink) {
   if (!h) return KC_ERR_INVALID;
   if (h->finished) return fail(h, KC_ERR_STATE, "finish called twice");
   CK(cudaSetDevice(h->cfg.device));
@@ -730,11 +766,31 @@ extern "C" int kc_finish(kc_handle *h) {
     if (rc) return rc;
   }
   if (!h->P) decide_partitions(h, 0);
-  return finish_count(h);
+  return finish_count(h, sink);
 }
+}  // namespace
+
+namespace {
+constexpr u32 SINK_SLICES = 8;
+
+// survivors [sink->copied, upto) are final once `ready` has happened on the main stream: send them to the host on the copy
+// stream while the main stream keeps counting
+int sink_copy(kc_handle *h, HostSink *sink, u64 upto, cudaEvent_t ready) {
+  const u64 n = std::min(upto, sink->cap), c = sink->copied;
+  if (n <= c) return KC_OK;
+  const int KW = h->KW;
+  CK(cudaStreamWaitEvent(h->s_copy, ready, 0));
+  CK(cudaMemcpyAsync(sink->keys + c * KW, (const u64 *)h->out_keys.p + c * KW, (n - c) * KW * 8, cudaMemcpyDeviceToHost, h->s_copy));
+  CK(cudaMemcpyAsync(sink->counts + c, (const uint16_t *)h->out_counts.p + c, (n - c) * 2, cudaMemcpyDeviceToHost, h->s_copy));
+  CK(cudaMemcpyAsync(sink->left + c, (const char *)h->out_left.p + c, n - c, cudaMemcpyDeviceToHost, h->s_copy));
+  CK(cudaMemcpyAsync(sink->right + c, (const char *)h->out_right.p + c, n - c, cudaMemcpyDeviceToHost, h->s_copy));
+  sink->copied = n;
+  return KC_OK;
+}
+}  // namespace
 
 // the count phase of one shard: every supermer that belongs to it is in h->blocks (own buckets) or h->rblocks (received)
-int finish_count(kc_handle *h) {
+int finish_count(kc_handle *h, HostSink *sink) {
   CK(cudaSetDevice(h->cfg.device));
   HostTimer ht;
   const u32 P = h->P;
@@ -877,12 +933,39 @@ int finish_count(kc_handle *h) {
     ca.tab_size = tab_size;
     ca.key_cap = key_cap;
     if (nitems) {
-      const unsigned grid = (unsigned)std::min<size_t>(nitems, (size_t)h->sms);
+      // With a host sink the device-built round runs as a few slices of the partition range: the survivors of slice g travel
+      // to the host while slice g+1 is being counted (the heavy list belongs to slice 0).
+      const u32 G = (first && sink && nitems >= 16u * (size_t)h->sms) ? SINK_SLICES : 1u;
+      while (h->ev_chunk.size() < G) {
+        cudaEvent_t e;
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->ev_chunk.push_back(e);
+      }
       CK(cudaEventRecord(h->ev_c, h->s_main));
-      RC(dispatch_count(h, wide, any_ctg, ca, smem, grid));
+      for (u32 g = 0; g < G; g++) {
+        CountArgs cg = ca;
+        const size_t lo = nitems * g / G, hi = nitems * (g + 1) / G;
+        cg.items = ca.items + lo;
+        cg.status = ca.status + lo;
+        cg.nitems = (u32)(hi - lo);
+        if (g) {
+          cg.heavy = nullptr;
+          cg.n_heavy = 0;
+        }
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)cg.nitems + cg.n_heavy, (size_t)h->sms);
+        RC(dispatch_count(h, wide, any_ctg, cg, smem, grid));
+        h->st.gpu_launches++;
+        h->st.n_insert_launches++;
+        if (G > 1) {
+          CK(cudaMemcpyAsync(ctr + CTR_WORDS * (g + 1), d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
+          CK(cudaEventRecord(h->ev_chunk[g], h->s_main));
+        }
+      }
       CK(cudaEventRecord(h->ev_d, h->s_main));
-      h->st.gpu_launches++;
-      h->st.n_insert_launches++;
+      for (u32 g = 0; G > 1 && g < G; g++) {
+        CK(cudaEventSynchronize(h->ev_chunk[g]));
+        RC(sink_copy(h, sink, ctr[CTR_WORDS * (g + 1) + CTR_SURV], h->ev_chunk[g]));
+      }
     }
     CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
     CK(cudaStreamSynchronize(h->s_main));
@@ -926,6 +1009,10 @@ int finish_count(kc_handle *h) {
   }
   CK(cudaEventRecord(e1, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
+  if (sink && !ctr[CTR_ERR]) {  // whatever the slices have not sent yet (retry rounds, unsliced runs)
+    RC(sink_copy(h, sink, ctr[CTR_SURV], e1));
+    CK(cudaStreamSynchronize(h->s_copy));
+  }
   h->st.ms_finish += elapsed(e0, e1);
   for (DevBuf *b : {&d_counters, &d_segs, &d_items, &d_status, &d_descs, &d_heavy, &d_ritems, &d_rstatus}) release(*b);
   if (ctr[CTR_ERR]) return fail(h, KC_ERR_OVERFLOW, "survivor output capacity exceeded");
@@ -1053,6 +1140,7 @@ extern "C" int kc_destroy(kc_handle *h) {
   pin_put(h->h_pin, h->pin_bytes);
   for (auto &p : h->pending) { dev_free(p.dir); dev_free(p.rec); }
   if (h->ev_fill) cudaEventDestroy(h->ev_fill);
+  for (auto e : h->ev_chunk) cudaEventDestroy(e);
   if (h->ev_x0) cudaEventDestroy(h->ev_x0);
   if (h->ev_x1) cudaEventDestroy(h->ev_x1);
   void kc_comm_destroy(kc_handle *);

@@ -277,7 +277,6 @@ int kc_exchange(kc_handle *h) {
 #endif
 }
 
-int finish_count(kc_handle *h);  // kc_api.cu
 
 // Local transport: all shards live in this process (handles[i] must be shard i of n). Exchange by peer copies, then count.
 extern "C" int kc_finish_local_group(kc_handle **hs, int32_t n) {

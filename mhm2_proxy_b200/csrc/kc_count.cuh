@@ -266,9 +266,9 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           u64 fwd[KW], rc[KW];
 #pragma unroll
           for (int i = 0; i < KW; i++) fwd[i] = (i < nw) ? fetch64(p, j + 32 * i) : 0ULL;
-#pragma unroll
-          for (int i = 0; i < KW; i++)
-            if (i == nw - 1) fwd[i] &= last_mask;
+          // word nw - 1 keeps only its k % 32 bases; nw is KW or KW - 1 (static indices: no local memory)
+          if (nw == KW) fwd[KW - 1] &= last_mask;
+          else if (KW >= 2) fwd[KW >= 2 ? KW - 2 : 0] &= last_mask;
           const int lcode = fetch_base(p, j - 1), lval = fetch_bit(pv, j - 1);
           const int rcode = fetch_base(p, j + k), rval = fetch_bit(pv, j + k);
           revcomp_words<KW>(fwd, rc, k);

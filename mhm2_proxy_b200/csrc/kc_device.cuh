@@ -79,12 +79,18 @@ __host__ __forceinline__ u64 revcomp64_host(u64 x) {
 template <int KW>
 __device__ __forceinline__ void revcomp_words(const u64 *in, u64 *out, int k) {
   const int nw = (k + 31) >> 5;  // words holding bases (kmer.cpp:488 last_long)
-  u64 t[KW];
+  u64 t[KW], rcw[KW];
 #pragma unroll
-  for (int i = 0; i < KW; i++) t[i] = 0;
+  for (int i = 0; i < KW; i++) rcw[i] = revcomp64(in[i]);
+  // t[nw - 1 - i] = rcw[i]. nw is KW or (k % 32 == 0) KW - 1: two compile-time candidates per word and a uniform select —
+  // a run-time index would push these arrays into local memory
+  const bool full = nw == KW;
 #pragma unroll
-  for (int i = 0; i < KW; i++)
-    if (i < nw) t[nw - 1 - i] = revcomp64(in[i]);
+  for (int i = 0; i < KW; i++) {
+    const u64 a = rcw[KW - 1 - i];
+    const u64 b = (KW - 2 - i >= 0) ? rcw[(KW - 2 - i >= 0) ? KW - 2 - i : 0] : 0ULL;
+    t[i] = full ? a : b;
+  }
   const int sh = (k & 31) ? 2 * (32 - (k & 31)) : 0;
 #pragma unroll
   for (int i = 0; i < KW; i++) {
@@ -141,10 +147,14 @@ __device__ __forceinline__ u64 canonical_mmer(u64 x, int m) {
 // (T > G > C > A); dmin_dyn = max((int)((1.0 - DYN_MIN_DEPTH) * count), dmin_thres) in IEEE fp64 — `frac` is the host's
 // (1.0 - dyn_min_depth), so 0.09999999999999998 for 0.9, and there is one multiply (no contraction possible).
 __host__ __device__ __forceinline__ char get_ext(const u32 *e, u32 count, int dmin_thres, double frac) {
+  // (value, index) kept in registers: indexing e[] with a run-time `top` would put the caller's counters in local memory
   int top = 3;  // start from T so that ties keep the larger letter
+  u32 best = e[3];
+#pragma unroll
   for (int i = 2; i >= 0; i--)
-    if (e[i] > e[top]) top = i;
+    if (e[i] > best) { best = e[i]; top = i; }
   u32 runner = 0;
+#pragma unroll
   for (int i = 0; i < 4; i++)
     if (i != top && e[i] > runner) runner = e[i];
 #ifdef __CUDA_ARCH__
@@ -153,9 +163,9 @@ __host__ __device__ __forceinline__ char get_ext(const u32 *e, u32 count, int dm
   int dmin_dyn = (int)(frac * (double)count);
 #endif
   if (dmin_dyn < dmin_thres) dmin_dyn = dmin_thres;
-  if ((int)e[top] < dmin_dyn) return 'X';
+  if ((int)best < dmin_dyn) return 'X';
   if ((int)runner >= dmin_dyn) return 'F';
-  return "ACGT"[top];
+  return top == 0 ? 'A' : top == 1 ? 'C' : top == 2 ? 'G' : 'T';
 }
 
 __device__ __forceinline__ u32 sat16(u64 v) { return v > 65535ULL ? 65535u : (u32)v; }

@@ -122,7 +122,7 @@ __device__ __forceinline__ void decode16_ascii(const uint4 v, int lo, int hi, u3
 }
 
 template <bool FILL, int NT>
-__global__ void __launch_bounds__(NT) parse_kernel(const ParseArgs a) {
+__global__ void __launch_bounds__(NT, (FILL ? 5 : 8) * 128 / NT) parse_kernel(const ParseArgs a) {
   extern __shared__ __align__(16) u32 smem_parse[];
   const int t = threadIdx.x;
   const Strided<NT> sb{smem_parse + t};                                   // [nsb] 2-bit bases, 16 per word, MSB first

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkcount_b200.so")
+LIB_PATH = os.environ.get("KCOUNT_B200_LIB") or os.path.join(_HERE, "libkcount_b200.so")  # override: A/B builds of the same ABI
 
 KC_OK = 0
 ERR_NAMES = {1: "INVALID", 2: "CUDA", 3: "STATE", 4: "NOMEM", 5: "BADCHAR", 6: "COMM", 7: "OVERFLOW"}
@@ -37,7 +37,7 @@ class KcStats(C.Structure):
 
 EXPORTS = [
     "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
-    "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
+    "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_to_host", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
 ]
 
@@ -68,6 +68,7 @@ def load_library():
     lib.kc_comm_unique_id.argtypes = [vp]
     lib.kc_comm_init.argtypes = [vp, vp]
     lib.kc_finish.argtypes = [vp]
+    lib.kc_finish_to_host.argtypes = [vp, vp, vp, vp, vp, u64, C.POINTER(u64)]
     lib.kc_finish_local_group.argtypes = [C.POINTER(vp), i32]
     lib.kc_num_survivors.argtypes = [vp, C.POINTER(u64)]
     lib.kc_copy_survivors.argtypes = [vp, vp, vp, vp, vp]
@@ -163,6 +164,14 @@ class KmerCounter:
 
     def finish(self):
         self._ck(self.lib.kc_finish(self.h), "kc_finish")
+
+    def finish_into(self, keys_ptr, counts_ptr, left_ptr, right_ptr, capacity):
+        """kc_finish_to_host: finish and deliver the table into caller-owned HOST buffers (raw pointers, `capacity` entries);
+        the copy overlaps the count stage. Returns the number of survivors."""
+        n = C.c_uint64()
+        self._ck(self.lib.kc_finish_to_host(self.h, C.c_void_p(keys_ptr), C.c_void_p(counts_ptr), C.c_void_p(left_ptr),
+                                            C.c_void_p(right_ptr), capacity, C.byref(n)), "kc_finish_to_host")
+        return n.value
 
     def num_survivors(self):
         n = C.c_uint64()

@@ -7,7 +7,7 @@ from mhm2_proxy_b200 import synth
 
 pytestmark = pytest.mark.gpu
 
-KS = [21, 31, 33, 55, 77, 99]
+KS = [21, 31, 32, 33, 55, 64, 77, 96, 99]
 
 
 def _oracle(k, rb, ro, **kw):
@@ -249,6 +249,35 @@ def test_reads_ascii_equals_packed(built, community):
         kc.finish()
         got = kc.survivors()
     _assert_same(got, _oracle(k, rb, ro), "ascii reads")
+
+
+@pytest.mark.parametrize("k,parts", [(21, 4096), (33, 3000), (55, 8)])
+def test_finish_to_host_equals_finish_plus_copy(built, community, k, parts):
+    """kc_finish_to_host (count stage in slices, survivors copied to the host while the next slice is counted) delivers
+    exactly the table of kc_finish + kc_copy_survivors; with too little room it reports OVERFLOW and the table stays
+    available on the device."""
+    from mhm2_proxy_b200 import kcount
+    rb, ro = synth.make_reads(12000, community, error_rate=0.01, seed=300 + k, n_rate=1e-3)
+    ref = _oracle(k, rb, ro)
+    nl = k // 32 + 1
+    cap = len(ref.counts) + 100
+    keys = np.zeros((cap, nl), dtype=np.uint64)
+    counts = np.zeros(cap, dtype=np.uint16)
+    left = np.zeros(cap, dtype=np.uint8)
+    right = np.zeros(cap, dtype=np.uint8)
+    with kcount.KmerCounter(k, num_partitions=parts) as kc:
+        kc.add_reads(rb, ro)
+        n = kc.finish_into(keys.ctypes.data, counts.ctypes.data, left.ctypes.data, right.ctypes.data, cap)
+        assert n == len(ref.counts)
+        assert kc.num_survivors() == n
+    order = np.lexsort(tuple(keys[:n, i] for i in range(nl - 1, -1, -1)))
+    _assert_same((keys[:n][order], counts[:n][order], left[:n][order], right[:n][order]), ref, f"finish_to_host k={k}")
+    small = max(1, n // 3)
+    with kcount.KmerCounter(k, num_partitions=parts) as kc:
+        kc.add_reads(rb, ro)
+        with pytest.raises(kcount.KcountError, match="OVERFLOW"):
+            kc.finish_into(keys.ctypes.data, counts.ctypes.data, left.ctypes.data, right.ctypes.data, small)
+        _assert_same(kc.survivors(), ref, f"table after a short host buffer k={k}")
 
 
 @pytest.mark.parametrize("n_shards,k", [(2, 21), (3, 33), (8, 31), (4, 99)])
