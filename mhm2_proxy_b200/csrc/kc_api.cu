@@ -60,11 +60,12 @@ struct kc_handle {
   int KW = 1, m = 15, w = 1;
   int smem_optin = 0, sms = 0;
   RecGeom geom;  // supermer record geometry for this k
-  u32 P = 0;  // partitions per shard (0 until the first add decides)
+  u32 P = 0;  // buckets per shard the parse stage uses (0 until the first add decides)
+  bool auto_merge = false;  // P was chosen by the library: fine-grained, neighbours are merged into work items at finish
   bool finished = false, has_ctg = false;
   cudaStream_t s_main = nullptr, s_copy = nullptr, s_comm = nullptr;
   std::vector<Pending> pending;
-  DevBuf d_meta, d_meta_all, d_tot;
+  DevBuf d_meta, d_meta_all, d_tot, d_scan, d_scan_comm;
   u64 *h_pin = nullptr;  // pinned scratch (PIN_BYTES): [0, PIN_META) bucket totals / counters, [PIN_META, ..) exchange metadata
   size_t pin_bytes = 0;
   cudaEvent_t ev_fill = nullptr, ev_x0 = nullptr, ev_x1 = nullptr;
@@ -338,14 +339,16 @@ void decide_partitions(kc_handle *h, u64 inst_estimate) {
     h->P = (u32)h->cfg.num_partitions;
   } else {
     u64 est = h->cfg.expected_instances ? h->cfg.expected_instances : inst_estimate;
-    // a partition should hold about 0.8 x key_cap distinct k-mers so that its whole table sits in one CTA's shared memory.
-    // distinct / instances is not known before counting: assume 0.25 (33x coverage with 0.5 % errors gives 0.13-0.19);
-    // a partition that turns out larger is re-run in sub-passes, never dropped.
+    // One work item of the count stage should hold about 0.8 x key_cap distinct k-mers so that its whole table sits in one
+    // CTA's shared memory. distinct / instances is not known before counting (0.13 at 33x coverage, > 0.5 at 2x), so the
+    // parse stage buckets at the granularity that would suit a ratio of 1, and finish_count measures the ratio on a
+    // sample of buckets and merges neighbouring buckets into items of the right size. A bucket that still turns out too
+    // large is re-run in hash sub-passes, never dropped.
     u32 tab, cap;
     table_geometry(h, false, false, tab, cap);
-    const double distinct = (double)est * 0.25;
-    u64 want = (u64)(distinct / (0.8 * cap)) + 1;
+    u64 want = (u64)((double)est / (0.8 * cap)) + 1;
     h->P = (u32)std::min<u64>(std::max<u64>(want, 1), 1u << 20);
+    h->auto_merge = true;
   }
   while ((u64)h->P * (u64)h->cfg.num_shards > (1ull << 22)) h->P >>= 1;
   // NOTE multi-shard: every shard must arrive at the same P (checked at exchange time); give all shards the same
@@ -353,28 +356,96 @@ void decide_partitions(kc_handle *h, u64 inst_estimate) {
   h->st.num_partitions = h->P;
 }
 
-// exclusive prefix sum of the per-bucket supermer counts -> index of each bucket's first record (one block; n is 10^5..10^6).
-// totals (optional): the first record of every destination shard's range, totals[n / P] = all of them
-__global__ void __launch_bounds__(1024) bucket_scan_kernel(const BucketHist *hist, u32 n, u64 *base, u32 P, u64 *totals) {
-  __shared__ u64 part[1024];
-  const u32 per = (n + 1023) / 1024, lo = min(n, threadIdx.x * per), hi = min(n, lo + per);
-  u64 sum = 0;
-  for (u32 i = lo; i < hi; i++) sum += hist[i].nsup;
-  part[threadIdx.x] = sum;
+// Exclusive prefix sum of the per-bucket supermer counts -> index of each bucket's first record, base[n] = total.
+// n is 10^4..4*10^6 (num_shards * P): three small launches — per-tile sums, scan of the (<= 1024) tile sums, per-tile scan.
+// totals (optional): the first record of every destination shard's range, totals[n / P] = all of them.
+constexpr u32 SCAN_TILE = 4096;  // 1024 threads x 4 entries
+
+__device__ __forceinline__ u64 block_exclusive_scan_1024(u64 v, u64 *warp_tot /* [32] shared */, u64 &block_total) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  u64 inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const u64 y = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += y;
+  }
+  if (lane == 31) warp_tot[wid] = inc;
   __syncthreads();
-  for (int d = 1; d < 1024; d <<= 1) {
-    const u64 v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
-    __syncthreads();
-    part[threadIdx.x] += v;
-    __syncthreads();
+  if (wid == 0) {
+    const u64 w = warp_tot[lane];
+    u64 wi = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const u64 y = __shfl_up_sync(0xffffffffu, wi, d);
+      if (lane >= d) wi += y;
+    }
+    warp_tot[lane] = wi - w;  // exclusive
+    if (lane == 31) warp_tot[32] = wi;
   }
-  u64 run = part[threadIdx.x] - sum;
-  for (u32 i = lo; i < hi; i++) {
-    base[i] = run;
-    if (totals && i % P == 0) totals[i / P] = run;
-    run += hist[i].nsup;
+  __syncthreads();
+  block_total = warp_tot[32];
+  return warp_tot[wid] + inc - v;
+}
+
+__global__ void __launch_bounds__(1024) scan_tile_sums_kernel(const BucketHist *hist, u32 n, u64 *tile_sum) {
+  __shared__ u64 wt[33];
+  const u32 i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+  u64 s = 0;
+#pragma unroll
+  for (u32 j = 0; j < 4; j++)
+    if (i0 + j < n) s += hist[i0 + j].nsup;
+  u64 tot;
+  block_exclusive_scan_1024(s, wt, tot);
+  if (threadIdx.x == 0) tile_sum[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024) scan_tile_offsets_kernel(u64 *tile_sum, u32 ntiles) {
+  __shared__ u64 wt[33];
+  const u64 v = threadIdx.x < ntiles ? tile_sum[threadIdx.x] : 0;
+  u64 tot;
+  const u64 ex = block_exclusive_scan_1024(v, wt, tot);
+  if (threadIdx.x < ntiles) tile_sum[threadIdx.x] = ex;
+  if (threadIdx.x == 0) tile_sum[ntiles] = tot;
+}
+
+__global__ void __launch_bounds__(1024) scan_apply_kernel(const BucketHist *hist, u32 n, const u64 *tile_off, u64 *base, u32 P,
+                                                          u64 *totals) {
+  __shared__ u64 wt[33];
+  const u32 i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
+  u32 c[4];
+  u64 s = 0;
+#pragma unroll
+  for (u32 j = 0; j < 4; j++) {
+    c[j] = i0 + j < n ? hist[i0 + j].nsup : 0u;
+    s += c[j];
   }
-  if (totals && threadIdx.x == 1023) totals[n / P] = part[1023];
+  u64 tot;
+  u64 run = tile_off[blockIdx.x] + block_exclusive_scan_1024(s, wt, tot);
+#pragma unroll
+  for (u32 j = 0; j < 4; j++) {
+    const u32 i = i0 + j;
+    if (i < n) {
+      base[i] = run;
+      if (totals && i % P == 0) totals[i / P] = run;
+    }
+    run += c[j];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const u64 all = tile_off[gridDim.x];
+    base[n] = all;
+    if (totals) totals[n / P] = all;
+  }
+}
+
+// base must hold n + 1 entries, tile_scratch (n + SCAN_TILE - 1) / SCAN_TILE + 1
+int bucket_scan(kc_handle *h, const BucketHist *hist, u32 n, u64 *base, u32 P, u64 *totals, u64 *tile_scratch, cudaStream_t st) {
+  const u32 ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  if (ntiles > 1024) return KC_ERR_INVALID;
+  scan_tile_sums_kernel<<<ntiles, 1024, 0, st>>>(hist, n, tile_scratch);
+  scan_tile_offsets_kernel<<<1, 1024, 0, st>>>(tile_scratch, ntiles);
+  scan_apply_kernel<<<ntiles, 1024, 0, st>>>(hist, n, tile_scratch, base, P, totals);
+  h->st.gpu_launches += 3;
+  return cudaGetLastError() == cudaSuccess ? KC_OK : KC_ERR_CUDA;
 }
 
 // Parse one batch that is already on the device. `bytes` may be a virtual base (bytes + start always lands inside
@@ -439,9 +510,9 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   CK(cudaGetLastError());
   CK(cudaEventRecord(h->ev_c, h->s_main));
   // bucket layout on the device: the host only needs the totals (allocation size, the range that goes to each shard)
-  CK(dev_alloc((void **)&blk.d_base, sizeof(u64) * NP));
-  bucket_scan_kernel<<<1, 1024, 0, h->s_main>>>(blk.d_hist, NP, blk.d_base, h->P, (u64 *)h->d_tot.p);
-  h->st.gpu_launches++;
+  CK(dev_alloc((void **)&blk.d_base, sizeof(u64) * ((size_t)NP + 1)));
+  RC(ensure(h, h->d_scan, sizeof(u64) * 1032));
+  RC(bucket_scan(h, blk.d_hist, NP, blk.d_base, h->P, (u64 *)h->d_tot.p, (u64 *)h->d_scan.p, h->s_main));
   CK(cudaMemcpyAsync(h->h_pin, h->d_tot.p, sizeof(u64) * (size_t)(N + 1), cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
   blk.dest_base.assign(h->h_pin, h->h_pin + N + 1);
@@ -826,21 +897,106 @@ int finish_count(kc_handle *h, HostSink *sink) {
   RC(ensure(h, d_descs, std::max<size_t>(nblk, 1) * sizeof(BlockDesc)));
   if (nblk) CK(cudaMemcpyAsync(d_descs.p, descs.data(), nblk * sizeof(BlockDesc), cudaMemcpyHostToDevice, h->s_main));
   CK(cudaMemsetAsync(d_status.p, 0, (size_t)P * sizeof(ItemStatus), h->s_main));
+  u64 *ctr = h->h_pin;  // pinned
   BuildArgs ba;
   ba.blocks = (const BlockDesc *)d_descs.p;
   ba.nblk = nblk;
   ba.P = P;
   ba.rw = h->geom.rw;
-  // Hash partitions are statistically alike; only outliers (skewed data: heavy-hitter partitions) are scheduled ahead
-  ba.heavy_thr = 2 * (sup_expected / P) + 1;
   ba.segs = (SegDesc *)d_segs.p;
   ba.items = (WorkItem *)d_items.p;
   ba.heavy = (u64 *)d_heavy.p;
   ba.counters = (u64 *)d_counters.p;
-  build_items_kernel<<<(P + 255) / 256, 256, 0, h->s_main>>>(ba);
+  // Automatic partitioning: how many neighbouring buckets make one work item? Probe: count (without emitting anything) a
+  // sample of single buckets spread over the partition space, take distinct / instances from it.
+  u32 merge = 1;
+  if (h->auto_merge && nblk && P > 1) {
+    u32 tab_size, key_cap;
+    table_geometry(h, false, any_ctg, tab_size, key_cap);
+    const int VWp = VR_NARROW + (any_ctg ? V_CTG : 0);
+    const size_t smem_p = count_smem_bytes(KW, VWp, tab_size, key_cap) + 8;
+    struct Probe { double mean = 0; u32 maxk = 0, over = 0; u64 inst = 0; u32 S = 0; };
+    // count (emitting nothing) a sample of S candidate items of g neighbouring buckets each, spread over the partition space
+    auto probe = [&](u32 g, Probe &pr) -> int {
+      const u32 nq = (P + g - 1) / g;
+      const u32 S = std::min<u32>(nq, 2u * (u32)h->sms);
+      ba.nitems = S;
+      ba.g = g;
+      ba.step = (nq / S) * g;
+      ba.heavy_thr = ~0ull;
+      build_items_kernel<<<(S + 255) / 256, 256, 0, h->s_main>>>(ba);
+      CountArgs pa;
+      memset(&pa, 0, sizeof(pa));
+      pa.items = (const WorkItem *)d_items.p;
+      pa.segs = (const SegDesc *)d_segs.p;
+      pa.status = (ItemStatus *)d_status.p;
+      pa.nitems = S;
+      pa.measure_only = 1;
+      pa.k = h->cfg.kmer_len;
+      pa.rw = h->geom.rw;
+      pa.nwb = h->geom.nwb;
+      pa.tab_size = tab_size;
+      pa.key_cap = key_cap;
+      pa.dmin_thres = h->cfg.dmin_thres;
+      pa.frac = 1.0 - h->cfg.dyn_min_depth;
+      pa.counters = (u64 *)d_counters.p;
+      RC(dispatch_count(h, false, any_ctg, pa, smem_p, std::min<unsigned>(S, (unsigned)h->sms)));
+      h->st.gpu_launches += 2;
+      std::vector<ItemStatus> pst(S);
+      CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
+      CK(cudaMemcpyAsync(pst.data(), d_status.p, (size_t)S * sizeof(ItemStatus), cudaMemcpyDeviceToHost, h->s_main));
+      CK(cudaStreamSynchronize(h->s_main));
+      u64 sum = 0;
+      for (auto &x : pst) {
+        sum += x.nkeys;
+        pr.maxk = std::max(pr.maxk, x.nkeys);
+        pr.over += x.overflow ? 1u : 0u;
+      }
+      pr.mean = (double)sum / S;
+      pr.inst = ctr[CTR_READ_INST] + ctr[CTR_CTG_INST];
+      pr.S = S;
+      CK(cudaMemsetAsync(d_counters.p, 0, CTR_WORDS * 8, h->s_main));
+      CK(cudaMemsetAsync(d_status.p, 0, (size_t)S * sizeof(ItemStatus), h->s_main));
+      return KC_OK;
+    };
+    // Key slots an item needs = its distinct k-mers + the slots same-key races leave unused; the second term does not grow
+    // with the item, so single buckets overstate what a merged item needs. Probe 1 (single buckets) gives a safe merge
+    // factor; probe 2 tries twice that on real candidates and is accepted only if every sampled item stays clear of the
+    // key store's capacity.
+    static const double fill = getenv("KC_TARGET_FILL") ? atof(getenv("KC_TARGET_FILL")) : 0.9;
+    Probe p1, p2;
+    RC(probe(1, p1));
+    u32 g_safe = 1;
+    if (!p1.over && p1.inst && p1.mean > 0) g_safe = (u32)std::min(64.0, std::max(1.0, std::floor(fill * key_cap / (1.1 * p1.mean))));
+    merge = g_safe;
+    const u32 g_try = std::min<u32>(64, std::min<u32>(P, 2 * g_safe));
+    if (!p1.over && g_try > g_safe) {
+      RC(probe(g_try, p2));
+      if (!p2.over && p2.maxk <= 0.95 * key_cap && 1.1 * p2.mean <= fill * key_cap) {
+        merge = g_try;
+      } else if (p2.over * 20 <= p2.S && p2.mean > p1.mean) {
+        // slots(g) ~ a + b g through the two measurements: largest g below g_try that keeps the margin (a few sampled
+        // items hitting the capacity only make the fitted slope a little too small)
+        const double bslope = (p2.mean - p1.mean) / (double)(g_try - 1), aoff = p1.mean - bslope;
+        const double g_fit = (fill * key_cap / 1.1 - aoff) / bslope;
+        merge = (u32)std::min<double>(g_try - 1, std::max<double>(g_safe, std::floor(g_fit)));
+      }
+    }
+    if (getenv("KC_TRACE"))
+      fprintf(stderr, "[kc_trace] probe: P %u key_cap %u | g=1: %.0f slots/item (%u items, %llu inst) -> safe %u | g=%u: mean %.0f max %u over %u"
+              " -> merge %u\n", P, key_cap, p1.mean, p1.S, (unsigned long long)p1.inst, g_safe, g_try, p2.mean, p2.maxk, p2.over, merge);
+    ht.lap("finish: partition probe");
+  }
+  const u32 NQ = (P + merge - 1) / merge;  // work items
+  h->st.num_partitions = NQ;
+  ba.nitems = NQ;
+  ba.g = merge;
+  ba.step = merge;
+  // Hash partitions are statistically alike; only outliers (skewed data: heavy-hitter partitions) are scheduled ahead
+  ba.heavy_thr = 2 * (sup_expected / NQ) + 1;
+  build_items_kernel<<<(NQ + 255) / 256, 256, 0, h->s_main>>>(ba);
   h->st.gpu_launches++;
   CK(cudaGetLastError());
-  u64 *ctr = h->h_pin;  // pinned
   CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
   if (ctr[CTR_ERR]) return fail(h, KC_ERR_INVALID, "a partition holds too many supermers: use more partitions");
@@ -917,7 +1073,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
       ca.status = (ItemStatus *)d_status.p;
       ca.heavy = (const u64 *)d_heavy.p;
       ca.n_heavy = n_heavy;
-      nitems = nblk ? P : 0;
+      nitems = nblk ? NQ : 0;
     } else {
       std::stable_sort(items.begin(), items.end(), [](const WorkItem &x, const WorkItem &y) { return x.nsup > y.nsup; });
       nitems = items.size();
@@ -1123,7 +1279,7 @@ extern "C" int kc_destroy(kc_handle *h) {
   for (auto &b : h->blocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   for (auto &b : h->rblocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_cursor, &h->d_meta, &h->d_meta_all,
-                    &h->d_tot, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
+                    &h->d_tot, &h->d_scan, &h->d_scan_comm, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
                     &h->pf_keys, &h->pf_vals};
   for (DevBuf *b : bufs) release(*b);
   if (h->ev_a) cudaEventDestroy(h->ev_a);

@@ -29,10 +29,11 @@ int make_rblock(kc_handle *h, BucketHist *dir, u32 *rec, u64 nsup, bool is_ctg, 
   b.rec = rec;
   b.d_hist = dir;
   b.tot_sup = nsup;
-  CK(dev_alloc((void **)&b.d_base, sizeof(u64) * h->P));
-  bucket_scan_kernel<<<1, 1024, 0, st>>>(dir, h->P, b.d_base, h->P, nullptr);
-  h->st.gpu_launches++;
-  CK(cudaGetLastError());
+  CK(dev_alloc((void **)&b.d_base, sizeof(u64) * ((size_t)h->P + 1)));
+  // scratch per stream: received blocks are scanned on the communication stream (or, local transport, on the main stream)
+  DevBuf &scratch = st == h->s_main ? h->d_scan : h->d_scan_comm;
+  RC(ensure(h, scratch, sizeof(u64) * 1032));
+  RC(bucket_scan(h, dir, h->P, b.d_base, h->P, nullptr, (u64 *)scratch.p, st));
   h->rblocks.push_back(std::move(b));
   return KC_OK;
 }

@@ -82,6 +82,7 @@ struct CountArgs {
   ItemStatus *status;
   const u64 *heavy;  // [n_heavy] (nsup << 32 | item index), heaviest first
   u32 nitems, n_heavy;
+  u32 measure_only;  // probe run: build the tables, report ItemStatus (distinct k-mers), emit nothing
   int k;
   int rw, nwb;     // record geometry (kc_parse.cuh)
   u32 tab_size, key_cap;  // tab_size u32 entries (multiple of 4)
@@ -124,6 +125,9 @@ __device__ __forceinline__ uint4 lds128_volatile(const void *p) {
   return v;
 }
 
+// 0..5 -> A C G T F X
+__device__ __forceinline__ char ext_char(u32 c) { return c < 4u ? (char)((0x54474341u >> (8u * c)) & 0xFFu) : (c == 4u ? 'F' : 'X'); }
+
 template <int KW, bool WIDE, bool CTG>
 __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a) {
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
@@ -136,6 +140,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   u32 *vals = (u32 *)(keys + (size_t)a.key_cap * KW);      // [key_cap * VW]
   SegDesc *segc = (SegDesc *)(vals + (size_t)a.key_cap * VW + ((a.key_cap * VW) & 1));  // [SEG_CACHE], 8-byte aligned
   __shared__ u64 s_obase[2];
+  __shared__ u32 s_ocur[2];
   __shared__ __align__(16) WorkItem s_work;
   __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed, s_widx;
   __shared__ u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];
@@ -198,6 +203,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
     for (u32 i = tid; i < prev * VW; i += CNT_THREADS) vals[i] = 0;  // counters of the slots the previous item used
     __syncthreads();
     const u32 nseg = it.seg_end - it.seg_begin;
+    u32 spare = 0xFFFFFFFFu;  // a dense entry this thread reserved but could not publish (same key claimed concurrently)
 
     for (u32 sg0 = 0; sg0 < nseg; sg0 += SEG_CACHE) {
       const int ns = (int)min((u32)SEG_CACHE, nseg - sg0);
@@ -310,11 +316,16 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             if (idx != 0xFFFFFFFFu) break;
             const u32 em = (bq.x == 0 ? 1u : 0u) | (bq.y == 0 ? 2u : 0u) | (bq.z == 0 ? 4u : 0u) | (bq.w == 0 ? 8u : 0u);
             if (em) {  // the key is not in the table (entries are never removed): claim the bucket's first empty entry
-              if (mine == 0xFFFFFFFFu) {  // reserve a dense entry, fill it, then publish it
-                mine = atomicAdd(&s_nkeys, 1u);
-                if (mine >= a.key_cap) {
-                  s_over = 1;
-                  break;
+              if (mine == 0xFFFFFFFFu) {  // reserve a dense entry (or reuse the one a lost race left us), fill it, publish it
+                if (spare != 0xFFFFFFFFu) {
+                  mine = spare;
+                  spare = 0xFFFFFFFFu;
+                } else {
+                  mine = atomicAdd(&s_nkeys, 1u);
+                  if (mine >= a.key_cap) {
+                    s_over = 1;
+                    break;
+                  }
                 }
 #pragma unroll
                 for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
@@ -331,7 +342,10 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             probes++;
             bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
           }
-          if (mine != 0xFFFFFFFFu && !claimed && mine < a.key_cap) keys[(size_t)mine * KW + KW - 1] = KEY_EMPTY;  // lost a same-key race
+          if (mine != 0xFFFFFFFFu && !claimed && mine < a.key_cap) {  // lost a same-key race: the entry stays ours for the next new key
+            keys[(size_t)mine * KW + KW - 1] = KEY_EMPTY;
+            spare = mine;
+          }
           if (idx == 0xFFFFFFFFu) continue;  // out of key slots; the item is re-run
           my_max_probe = max(my_max_probe, probes);
           u32 *v = vals + (size_t)idx * VW;
@@ -380,11 +394,12 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         ((uint4 *)&s_work)[1] = nx1;
         s_widx = nx_idx;
       }
-      if (over || wide_needed) atomicAdd((unsigned long long *)&a.counters[CTR_RETRY], 1ull);
+      if ((over || wide_needed) && !a.measure_only) atomicAdd((unsigned long long *)&a.counters[CTR_RETRY], 1ull);
     }
-    if (over || wide_needed) continue;
+    if (over || wide_needed || a.measure_only) continue;
 
     // ---- e. depth filter, extension choice, compaction (kcount_cpu.cpp:490-528) ----
+    u32 n_occ = 0, n_sv = 0, n_pf = 0;
     for (u32 b0 = 0; b0 < n; b0 += CNT_THREADS) {
       const u32 idx = b0 + (u32)tid;
       const u64 *kp = keys + (size_t)idx * KW;
@@ -441,59 +456,88 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         }
       }
       const bool pf = a.pf_keys && occ && rcount > 0;  // k-mers seen in reads (the table as it stands after the reads pass)
-      const u32 occ_mask = __ballot_sync(0xffffffffu, occ);
+      // verdict of this key, parked in the index table (no longer needed: insertion is over) until output space is reserved
+      if (idx < n) {
+        const u32 lc = le == 'A' ? 0u : le == 'C' ? 1u : le == 'G' ? 2u : le == 'T' ? 3u : le == 'F' ? 4u : 5u;
+        const u32 rc_ = re == 'A' ? 0u : re == 'C' ? 1u : re == 'G' ? 2u : re == 'T' ? 3u : re == 'F' ? 4u : 5u;
+        tab[idx] = (count & 0xFFFFu) | (lc << 16) | (rc_ << 19) | (survive ? 1u << 22 : 0u) | (pf ? 1u << 23 : 0u);
+      }
+      n_occ += occ ? 1u : 0u;
+      n_sv += survive ? 1u : 0u;
+      n_pf += pf ? 1u : 0u;
+    }
+    // one reservation of output space per item (a global atomic with result costs ~1 us: not once per 1024 keys)
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+      n_occ += __shfl_xor_sync(0xffffffffu, n_occ, d);
+      n_sv += __shfl_xor_sync(0xffffffffu, n_sv, d);
+      n_pf += __shfl_xor_sync(0xffffffffu, n_pf, d);
+    }
+    if (lane == 0) { warp_c[wid] = n_sv; warp_p[wid] = n_pf; if (n_occ) atomicAdd(&s_live, n_occ); }
+    __syncthreads();
+    if (wid == 0) {
+      u32 c = warp_c[lane], p = warp_p[lane];
+#pragma unroll
+      for (int d = 16; d; d >>= 1) {
+        c += __shfl_xor_sync(0xffffffffu, c, d);
+        p += __shfl_xor_sync(0xffffffffu, p, d);
+      }
+      if (lane == 0) {
+        s_obase[0] = c ? atomicAdd(&a.counters[CTR_SURV], (u64)c) : 0ull;
+        s_obase[1] = p ? atomicAdd(&a.counters[CTR_PF], (u64)p) : 0ull;
+        s_ocur[0] = 0;
+        s_ocur[1] = 0;
+      }
+    }
+    __syncthreads();
+    for (u32 b0 = 0; b0 < n; b0 += CNT_THREADS) {
+      const u32 idx = b0 + (u32)tid;
+      const u32 res = idx < n ? tab[idx] : 0u;
+      const bool survive = (res >> 22) & 1u, pf = (res >> 23) & 1u;
+      const u64 *kp = keys + (size_t)idx * KW;
       const u32 sv_mask = __ballot_sync(0xffffffffu, survive);
-      const u32 pf_mask = __ballot_sync(0xffffffffu, pf);
-      if (lane == 0 && occ_mask) atomicAdd(&s_live, (u32)__popc(occ_mask));
-      if (lane == 0) { warp_c[wid] = __popc(sv_mask); warp_p[wid] = __popc(pf_mask); }
-      __syncthreads();
-      if (wid == 0) {  // one warp scans the 32 warp totals and reserves output space for the block
-        const u32 c = warp_c[lane], p = warp_p[lane];
-        u32 ic = c, ip = p;
+      if (sv_mask) {
+        u32 wbase = 0;
+        if (lane == 0) wbase = atomicAdd(&s_ocur[0], (u32)__popc(sv_mask));
+        wbase = __shfl_sync(0xffffffffu, wbase, 0);
+        if (survive) {
+          const u64 o = s_obase[0] + wbase + __popc(sv_mask & ((1u << lane) - 1u));
+          if (o < a.out_cap) {
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const u32 yc = __shfl_up_sync(0xffffffffu, ic, d), yp = __shfl_up_sync(0xffffffffu, ip, d);
-          if (lane >= d) { ic += yc; ip += yp; }
-        }
-        warp_c[lane] = ic - c;
-        warp_p[lane] = ip - p;
-        const u32 totc = __shfl_sync(0xffffffffu, ic, 31), totp = __shfl_sync(0xffffffffu, ip, 31);
-        if (lane == 0) {
-          s_obase[0] = totc ? atomicAdd(&a.counters[CTR_SURV], (u64)totc) : 0ull;
-          s_obase[1] = totp ? atomicAdd(&a.counters[CTR_PF], (u64)totp) : 0ull;
-        }
-      }
-      __syncthreads();
-      if (survive) {
-        const u64 o = s_obase[0] + warp_c[wid] + __popc(sv_mask & ((1u << lane) - 1u));
-        if (o < a.out_cap) {
-#pragma unroll
-          for (int i = 0; i < KW; i++) a.out_keys[o * KW + i] = kp[i];
-          a.out_counts[o] = (uint16_t)count;
-          a.out_left[o] = le;
-          a.out_right[o] = re;
-        } else {
-          a.counters[CTR_ERR] = 1;
-        }
-      }
-      if (pf) {
-        const u64 o = s_obase[1] + warp_p[wid] + __popc(pf_mask & ((1u << lane) - 1u));
-        if (o < a.pf_cap) {
-          const u32 *v = vals + (size_t)idx * VW;
-#pragma unroll
-          for (int i = 0; i < KW; i++) a.pf_keys[o * KW + i] = kp[i];
-          uint16_t *ov = a.pf_vals + o * 9;
-          ov[0] = (uint16_t)rcount;
-          if (WIDE) {
-#pragma unroll
-            for (int i = 0; i < 4; i++) { ov[1 + i] = (uint16_t)sat16(v[i]); ov[5 + i] = (uint16_t)sat16(v[5 + i]); }
+            for (int i = 0; i < KW; i++) a.out_keys[o * KW + i] = kp[i];
+            a.out_counts[o] = (uint16_t)(res & 0xFFFFu);
+            a.out_left[o] = ext_char((res >> 16) & 7u);
+            a.out_right[o] = ext_char((res >> 19) & 7u);
           } else {
-            const u32 w0 = v[0], w1 = v[1], w2 = v[2], w3 = v[3], w4 = v[4];
-            ov[1] = (uint16_t)w0; ov[2] = (uint16_t)(w0 >> 16); ov[3] = (uint16_t)w1; ov[4] = (uint16_t)(w1 >> 16);
-            ov[5] = (uint16_t)(w2 >> 16); ov[6] = (uint16_t)w3; ov[7] = (uint16_t)(w3 >> 16); ov[8] = (uint16_t)w4;
+            a.counters[CTR_ERR] = 1;
           }
-        } else {
-          a.counters[CTR_ERR] = 1;
+        }
+      }
+      const u32 pf_mask = __ballot_sync(0xffffffffu, pf);
+      if (pf_mask) {
+        u32 wbase = 0;
+        if (lane == 0) wbase = atomicAdd(&s_ocur[1], (u32)__popc(pf_mask));
+        wbase = __shfl_sync(0xffffffffu, wbase, 0);
+        if (pf) {
+          const u64 o = s_obase[1] + wbase + __popc(pf_mask & ((1u << lane) - 1u));
+          if (o < a.pf_cap) {
+            const u32 *v = vals + (size_t)idx * VW;
+#pragma unroll
+            for (int i = 0; i < KW; i++) a.pf_keys[o * KW + i] = kp[i];
+            uint16_t *ov = a.pf_vals + o * 9;
+            if (WIDE) {
+              ov[0] = (uint16_t)sat16((u64)v[0] + v[1] + v[2] + v[3] + v[4]);
+#pragma unroll
+              for (int i = 0; i < 4; i++) { ov[1 + i] = (uint16_t)sat16(v[i]); ov[5 + i] = (uint16_t)sat16(v[5 + i]); }
+            } else {
+              const u32 w0 = v[0], w1 = v[1], w2 = v[2], w3 = v[3], w4 = v[4];
+              ov[0] = (uint16_t)sat16((u64)(w0 & 0xFFFFu) + (w0 >> 16) + (w1 & 0xFFFFu) + (w1 >> 16) + (w2 & 0xFFFFu));
+              ov[1] = (uint16_t)w0; ov[2] = (uint16_t)(w0 >> 16); ov[3] = (uint16_t)w1; ov[4] = (uint16_t)(w1 >> 16);
+              ov[5] = (uint16_t)(w2 >> 16); ov[6] = (uint16_t)w3; ov[7] = (uint16_t)(w3 >> 16); ov[8] = (uint16_t)w4;
+            }
+          } else {
+            a.counters[CTR_ERR] = 1;
+          }
         }
       }
     }
@@ -510,7 +554,9 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
 // the heavy list. Totals (instances from reads / contigs, supermers) are reduced into counters[].
 struct BuildArgs {
   const BlockDesc *blocks;
-  u32 nblk, P;
+  u32 nblk, P;   // P = buckets of this shard (the granularity the parse stage bucketed at)
+  u32 nitems;    // item q covers buckets [q * step, min(q * step + g, P)): step == g merges neighbours (their records are
+  u32 g, step;   //   contiguous inside every batch); step > g samples the partition space (probe run)
   int rw;
   u64 heavy_thr;  // nsup above this -> heavy
   SegDesc *segs;  // [P * nblk]
@@ -522,23 +568,25 @@ struct BuildArgs {
 __global__ void __launch_bounds__(256) build_items_kernel(const BuildArgs a) {
   const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
   u64 nsup = 0, ri = 0, ci = 0;
-  if (p < a.P) {
+  if (p < a.nitems) {
     const u32 s0 = p * a.nblk;
+    const u32 b_lo = p * a.step, b_hi = min(b_lo + a.g, a.P);
     u32 cnt = 0;
     for (u32 j = 0; j < a.nblk; j++) {
       const BlockDesc d = a.blocks[j];
-      const u32 bu = d.first + p;
-      const BucketHist hh = d.hist[bu];
-      if (!hh.nsup) continue;
+      const u64 r0 = d.base[d.first + b_lo], r1 = d.base[d.first + b_hi];  // base[] has one entry past the last bucket
+      if (r1 == r0) continue;
+      u64 ninst = 0;
+      for (u32 b = b_lo; b < b_hi; b++) ninst += d.hist[d.first + b].ninst;
       SegDesc sd;
-      sd.rec = d.rec + (size_t)d.base[bu] * a.rw;
-      sd.nsup = hh.nsup;
+      sd.rec = d.rec + (size_t)r0 * a.rw;
+      sd.nsup = (u32)(r1 - r0);
       sd.is_ctg = d.is_ctg;
       sd.sup0 = (u32)nsup;
       sd.pad = 0;
       a.segs[s0 + cnt++] = sd;
-      nsup += hh.nsup;
-      if (d.is_ctg) ci += hh.ninst; else ri += hh.ninst;
+      nsup += r1 - r0;
+      if (d.is_ctg) ci += ninst; else ri += ninst;
     }
     WorkItem it;
     it.seg_begin = s0;
