@@ -182,8 +182,10 @@ class HostOut:
         self.right = torch.empty(self.cap, dtype=torch.uint8, pin_memory=True)
 
 
-def one_pass(kcount, k, args, rank, world, dev, mode, tb, to, d_b, d_o, uid, hout=None):
-    """One kcount round at one k. mode 'device': reads already in HBM; 'host': pinned host buffers + D2H of survivors."""
+def one_pass(kcount, k, args, rank, world, dev, mode, tb, to, d_b, d_o, uid, hout=None, resident=None):
+    """One kcount round at one k. mode 'device': reads already in HBM; 'host': the step's reads come from pinned host buffers
+    (uploaded once per step by kc_reads_create, shared by the k rounds as the reference shares its PackedReads) and the table
+    goes back to pinned host memory."""
     n = to.numel() - 1
     inst_hint = n * (READ_LEN - k - 1)
     kc = kcount.KmerCounter(k, num_shards=world, shard_id=rank, device=dev, expected_instances=inst_hint,
@@ -193,6 +195,8 @@ def one_pass(kcount, k, args, rank, world, dev, mode, tb, to, d_b, d_o, uid, hou
             kc.comm_init(uid)
         if mode == "device":
             kc.add_reads_device(d_b.data_ptr(), d_o.data_ptr(), n, d_b.numel(), READ_LEN)
+        elif resident is not None:
+            kc.add_reads_resident(resident)
         else:
             kc.add_reads_ptr(tb.data_ptr(), to.data_ptr(), n)
         d2h = 0
@@ -245,18 +249,28 @@ def run_ours(args):
 
     hout = HostOut(n_reads)
 
+    def one_step(mode):
+        """All k rounds over one set of reads. End-to-end mode: host -> device copy of the reads (once; HBM keeps them for
+        every k), every round's table back to the host."""
+        res = None
+        if mode == "host" and not args.e2e_per_round_upload:
+            res = kcount.ResidentReads(tb.data_ptr(), to.data_ptr(), to.numel() - 1, device=local)
+        try:
+            return [one_pass(kcount, k, args, rank, world, local, mode, tb, to, d_b, d_o, uid, hout, res) for k in args.ks]
+        finally:
+            if res is not None:
+                res.close()
+
     def timed(mode, steps, warmup, sampler=None):
         for _ in range(warmup):
-            for k in args.ks:
-                one_pass(kcount, k, args, rank, world, local, mode, tb, to, d_b, d_o, uid, hout)
+            one_step(mode)
         sync()
         if sampler:
             sampler.start()
         stats = []
         t_start = time.perf_counter()
         for _ in range(steps):
-            for k in args.ks:
-                stats.append(one_pass(kcount, k, args, rank, world, local, mode, tb, to, d_b, d_o, uid, hout))
+            stats.extend(one_step(mode))
         sync()
         el = time.perf_counter() - t_start
         clocks = sampler.stop() if sampler else None
@@ -320,7 +334,7 @@ def run_ours(args):
         cores = os.cpu_count() or 1
         cpu = reference_rate(tb, to, min(n_reads, args.ref_reads or 40_000 * cores), args.ks, cores)
     value = inst_all / el
-    h2d = (tb.numel() + to.numel() * 8) * len(args.ks)
+    h2d = (tb.numel() + to.numel() * 8) * (len(args.ks) if args.e2e_per_round_upload else 1)
     d2h = sum(s["d2h_bytes"] for s in stats2) / e2e_steps
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -329,7 +343,10 @@ def run_ours(args):
         "timing": "wall clock around K steps, torch.cuda.synchronize (+barrier) on both sides, max over ranks; per-kernel times "
                   "are CUDA events on the library's stream",
         "e2e": {"value": inst2_all / el2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h),
-                "steps": e2e_steps, "ms_per_step": 1000 * el2 / e2e_steps},
+                "steps": e2e_steps, "ms_per_step": 1000 * el2 / e2e_steps,
+                "path": ("kc_add_reads per k round" if args.e2e_per_round_upload else
+                         "kc_reads_create once per step (pinned host reads -> HBM, shared by the k rounds)") +
+                        " + kc_add_reads_resident + kc_finish_to_host (table -> pinned host memory) per k round"},
         "gpu_launches": int(sum(s["gpu_launches"] for s in stats)),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "launches": launches[dom],
@@ -366,6 +383,8 @@ def main():
     ap.add_argument("--ks", type=lambda s: tuple(int(x) for x in s.split(",")), default=C2_KS)
     ap.add_argument("--partitions", type=int, default=0)
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=2)
+    ap.add_argument("--e2e-per-round-upload", dest="e2e_per_round_upload", action="store_true",
+                    help="end-to-end arm: copy the reads host->device again for every k round (kc_add_reads) instead of once per step")
     ap.add_argument("--ref-reads", dest="ref_reads", type=int, default=0, help="reads in the CPU sample (default 40k per core)")
     ap.add_argument("--ref-warm", dest="ref_warm", action="store_true", help="also run warm-up passes in --impl reference")
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true", help="skip the cpu_baseline leg")

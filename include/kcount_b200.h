@@ -96,6 +96,17 @@ int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *offsets, ui
 /* same, DEVICE pointers already resident on cfg.device (no copy). total_bytes = offsets[n_reads]. */
 int kc_add_reads_device(kc_handle *h, const uint8_t *d_bytes, const uint64_t *d_offsets, uint64_t n_reads, uint64_t total_bytes,
                         uint32_t max_read_len);
+/* PackedReads kept in HBM across the k rounds of one job: contigging.cpp:115-118 runs analyze_kmers once per k over the same
+ * packed_reads_list, which the reference keeps in host memory for the whole run (main.cpp:169, packed_reads.hpp:120-167).
+ * kc_reads_create uploads bytes/offsets (same layout as kc_add_reads; offsets[0] must be 0) asynchronously in batches and
+ * returns at once; kc_add_reads_resident parses them into a handle (any number of handles, one after the other) and, used
+ * right after the create, overlaps the upload batch by batch. The host arrays must stay valid until the first
+ * kc_add_reads_resident returned (or kc_reads_destroy). 180 GB of HBM hold the reads of any single-node run. */
+typedef struct kc_reads kc_reads;
+int kc_reads_create(int32_t device, const uint8_t *bytes, const uint64_t *offsets, uint64_t n_reads, int32_t batch_reads,
+                    kc_reads **out);
+int kc_add_reads_resident(kc_handle *h, kc_reads *reads);
+int kc_reads_destroy(kc_reads *reads);
 /* add_ctg_kmers' loop -> process_seq(ctg.seq, ctg.get_uint16_t_depth()) (kcount.cpp:123-130, contigs.hpp:57-66).
  * seqs = ASCII ACGTN (host), offsets[n+1], depths = Contig::depth doubles. Any length; long contigs are tiled. */
 int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs);

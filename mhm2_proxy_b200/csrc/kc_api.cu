@@ -691,6 +691,101 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
   return KC_OK;
 }
 
+// ---- PackedReads resident in HBM across the k rounds of a job ----
+struct kc_reads {
+  int device = 0;
+  uint8_t *d_bytes = nullptr;
+  u64 *d_offsets = nullptr;
+  u64 n_reads = 0, total_bytes = 0, batch = 0;
+  cudaStream_t stream = nullptr;
+  std::vector<cudaEvent_t> ready;   // per batch: its bytes and offsets have arrived
+  std::vector<u32> max_len;         // per batch
+  std::vector<u64> h_offsets;       // kept only when some read is longer than one parse tile (host-side tiling needs them)
+  std::string err;
+};
+
+extern "C" int kc_reads_create(int32_t device, const uint8_t *bytes, const uint64_t *offsets, uint64_t n_reads, int32_t batch_reads,
+                               kc_reads **out) {
+  if (!out) return KC_ERR_INVALID;
+  *out = nullptr;
+  if (!bytes || !offsets || offsets[0] != 0) return KC_ERR_INVALID;
+  kc_handle *h = nullptr;  // CK reports into a handle; there is none here
+  kc_reads *r = new kc_reads();
+  *out = r;
+  r->device = device;
+  r->n_reads = n_reads;
+  r->total_bytes = offsets[n_reads];
+  CK(cudaSetDevice(device));
+  CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+  CK(dev_alloc((void **)&r->d_bytes, r->total_bytes + 64));
+  CK(dev_alloc((void **)&r->d_offsets, (n_reads + 1) * 8));
+  u64 batch = batch_reads > 0 ? (u64)batch_reads : (2ull << 20);
+  const u64 avg = std::max<u64>(1, r->total_bytes / std::max<u64>(n_reads, 1));
+  batch = std::max<u64>(1, std::min<u64>(batch, (1ull << 30) / avg));
+  r->batch = batch;
+  const u64 nb = (n_reads + batch - 1) / batch;
+  bool any_long = false;
+  for (u64 bi = 0; bi < nb; bi++) {  // all copies are queued first; the length scan below runs while they are in flight
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    CK(cudaMemcpyAsync(r->d_bytes + offsets[r0], bytes + offsets[r0], offsets[r1] - offsets[r0], cudaMemcpyHostToDevice, r->stream));
+    CK(cudaMemcpyAsync(r->d_offsets + r0, offsets + r0, (r1 - r0 + 1) * 8, cudaMemcpyHostToDevice, r->stream));
+    cudaEvent_t e;
+    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(cudaEventRecord(e, r->stream));
+    r->ready.push_back(e);
+  }
+  for (u64 bi = 0; bi < nb; bi++) {
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    u64 ml = 0;
+    for (u64 i = r0; i < r1; i++) ml = std::max<u64>(ml, offsets[i + 1] - offsets[i]);
+    r->max_len.push_back((u32)std::min<u64>(ml, 0xFFFFFFFFu));
+    any_long = any_long || ml > (u64)SEG_MAX;
+  }
+  if (any_long) r->h_offsets.assign(offsets, offsets + n_reads + 1);
+  return KC_OK;
+}
+
+extern "C" int kc_reads_destroy(kc_reads *r) {
+  if (!r) return KC_OK;
+  cudaSetDevice(r->device);
+  if (r->stream) cudaStreamSynchronize(r->stream);
+  for (auto e : r->ready) cudaEventDestroy(e);
+  dev_free(r->d_bytes);
+  dev_free(r->d_offsets);
+  if (r->stream) cudaStreamDestroy(r->stream);
+  delete r;
+  return KC_OK;
+}
+
+extern "C" int kc_add_reads_resident(kc_handle *h, kc_reads *r) {
+  if (!h || !r) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "add after finish");
+  if (r->device != h->cfg.device) return fail(h, KC_ERR_INVALID, "reads live on device %d, the handle on %d", r->device, h->cfg.device);
+  if (r->n_reads == 0) return KC_OK;
+  CK(cudaSetDevice(h->cfg.device));
+  const int k = h->cfg.kmer_len;
+  const u64 k1 = (u64)k + 1;
+  decide_partitions(h, r->total_bytes > r->n_reads * k1 ? r->total_bytes - r->n_reads * k1 : 0);
+  for (u64 bi = 0; bi < r->ready.size(); bi++) {
+    const u64 r0 = bi * r->batch, r1 = std::min<u64>(r->n_reads, r0 + r->batch);
+    CK(cudaStreamWaitEvent(h->s_main, r->ready[bi], 0));  // first use right after kc_reads_create overlaps the upload
+    int rc;
+    if (r->max_len[bi] <= (u32)SEG_MAX) {
+      rc = parse_batch(h, r->d_bytes, r->d_offsets + r0, nullptr, nullptr, nullptr, r1 - r0, (int)r->max_len[bi], false, false);
+    } else {
+      std::vector<u64> ss;
+      std::vector<u32> sl;
+      std::vector<uint16_t> sd;
+      for (u64 i = r0; i < r1; i++) tile_sequence(r->h_offsets[i], r->h_offsets[i + 1] - r->h_offsets[i], k, SEG_MAX, 1, ss, sl, sd);
+      rc = parse_segments(h, r->d_bytes, ss, sl, sd, SEG_MAX, false, false);
+    }
+    if (rc) return rc;
+  }
+  h->st.num_seqs += r->n_reads;
+  h->st.num_bases += r->total_bytes;
+  return KC_OK;
+}
+
 namespace {
 
 // ASCII sequences (ACGTN, lower case = low quality): contigs with their depths, or reads as count_kmers hands them to

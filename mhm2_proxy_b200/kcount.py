@@ -36,7 +36,7 @@ class KcStats(C.Structure):
 
 
 EXPORTS = [
-    "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
+    "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_reads_create", "kc_add_reads_resident", "kc_reads_destroy", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
     "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_to_host", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
 ]
@@ -68,6 +68,9 @@ def load_library():
     lib.kc_comm_unique_id.argtypes = [vp]
     lib.kc_comm_init.argtypes = [vp, vp]
     lib.kc_finish.argtypes = [vp]
+    lib.kc_reads_create.argtypes = [i32, vp, vp, u64, i32, C.POINTER(vp)]
+    lib.kc_add_reads_resident.argtypes = [vp, vp]
+    lib.kc_reads_destroy.argtypes = [vp]
     lib.kc_finish_to_host.argtypes = [vp, vp, vp, vp, vp, u64, C.POINTER(u64)]
     lib.kc_finish_local_group.argtypes = [C.POINTER(vp), i32]
     lib.kc_num_survivors.argtypes = [vp, C.POINTER(u64)]
@@ -165,6 +168,10 @@ class KmerCounter:
     def finish(self):
         self._ck(self.lib.kc_finish(self.h), "kc_finish")
 
+    def add_reads_resident(self, reads):
+        """Parse reads that a ResidentReads object holds (or is still uploading) in HBM."""
+        self._ck(self.lib.kc_add_reads_resident(self.h, reads.r), "kc_add_reads_resident")
+
     def finish_into(self, keys_ptr, counts_ptr, left_ptr, right_ptr, capacity):
         """kc_finish_to_host: finish and deliver the table into caller-owned HOST buffers (raw pointers, `capacity` entries);
         the copy overlaps the count stage. Returns the number of survivors."""
@@ -230,6 +237,36 @@ class KmerCounter:
             self.close()
         except Exception:
             pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+class ResidentReads:
+    """kc_reads: PackedRead bytes + offsets uploaded once (asynchronously) and shared by the k rounds of a job. Takes raw HOST
+    pointers (pinned memory copies fastest) or numpy arrays, which must stay alive until the first add_reads_resident."""
+
+    def __init__(self, bytes_, offsets, n_reads=None, device=0, batch_reads=0):
+        self.lib = load_library()
+        if isinstance(bytes_, np.ndarray):
+            self._keep = (np.ascontiguousarray(bytes_, dtype=np.uint8), np.ascontiguousarray(offsets, dtype=np.uint64))
+            n_reads = len(self._keep[1]) - 1
+            bp, op = _ptr(self._keep[0]), _ptr(self._keep[1])
+        else:
+            bp, op = C.c_void_p(bytes_), C.c_void_p(offsets)
+        self.r = C.c_void_p()
+        rc = self.lib.kc_reads_create(device, bp, op, n_reads, batch_reads, C.byref(self.r))
+        if rc != KC_OK:
+            self.close()
+            raise KcountError(f"kc_reads_create failed ({ERR_NAMES.get(rc, rc)})")
+
+    def close(self):
+        if self.r:
+            self.lib.kc_reads_destroy(self.r)
+            self.r = C.c_void_p()
 
     def __enter__(self):
         return self

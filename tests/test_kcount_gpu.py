@@ -251,6 +251,24 @@ def test_reads_ascii_equals_packed(built, community):
     _assert_same(got, _oracle(k, rb, ro), "ascii reads")
 
 
+def test_resident_reads_shared_by_rounds(built, community):
+    """kc_reads_create uploads the PackedRead bytes once; two k rounds (and a round with long, tiled reads) parse them from
+    HBM and give the tables kc_add_reads gives."""
+    from mhm2_proxy_b200 import kcount
+    rb, ro = synth.make_reads(9000, community, error_rate=0.01, seed=11, n_rate=1e-3, var_len=True)
+    with kcount.ResidentReads(rb, ro, batch_reads=2500) as rr:
+        for k in (21, 55):
+            with kcount.KmerCounter(k, num_partitions=0) as kc:
+                kc.add_reads_resident(rr)
+                kc.finish()
+                _assert_same(kc.survivors(), _oracle(k, rb, ro), f"resident reads k={k}")
+    lb, lo = synth.make_reads(300, community, read_len=900, error_rate=0.01, seed=12)  # longer than one parse tile
+    with kcount.ResidentReads(lb, lo, batch_reads=100) as rr, kcount.KmerCounter(33, num_partitions=5) as kc:
+        kc.add_reads_resident(rr)
+        kc.finish()
+        _assert_same(kc.survivors(), _oracle(33, lb, lo), "resident long reads")
+
+
 @pytest.mark.parametrize("k,parts", [(21, 4096), (33, 3000), (55, 8)])
 def test_finish_to_host_equals_finish_plus_copy(built, community, k, parts):
     """kc_finish_to_host (count stage in slices, survivors copied to the host while the next slice is counted) delivers
