@@ -1,0 +1,88 @@
+"""Size-independent properties at BASELINE.json's full C2 size (13.33 M reads, 2 Gbase), where the CPU oracle would take
+minutes: the table must not depend on batching, partitioning, sharding or on how the reads reached the device, and must
+satisfy the invariants of the reference's output (kcount_cpu.cpp:490-528)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+
+N_READS = 13_333_334
+K = 21
+
+
+def _revcomp21(keys):
+    """reverse complement of left-aligned 2-bit k-mers (k = 21) held in u64, numpy restatement of kmer.cpp:485-505"""
+    x = keys.copy()
+    m1, m2 = np.uint64(0x3333333333333333), np.uint64(0x0F0F0F0F0F0F0F0F)
+    x = ((x >> np.uint64(2)) & m1) | ((x & m1) << np.uint64(2))
+    x = ((x >> np.uint64(4)) & m2) | ((x & m2) << np.uint64(4))
+    x = x.byteswap()  # 2-bit groups now in reverse order over all 32 positions
+    x = ~x
+    return x << np.uint64(2 * (32 - K))
+
+
+def _sorted_table(keys, counts, left, right):
+    o = np.argsort(keys[:, 0], kind="stable")
+    return keys[o, 0], counts[o], left[o], right[o]
+
+
+@pytest.fixture(scope="module")
+def reads(built):
+    import bench
+    tb, to = bench.gen_reads(N_READS, seed=0xB200_0002)
+    return tb.numpy(), to.numpy().astype(np.uint64)
+
+
+def test_full_size_invariants_and_invariance(built, reads):
+    from mhm2_proxy_b200 import kcount
+    rb, ro = reads
+    lens = np.diff(ro.astype(np.int64))
+    expect_inst = int(np.maximum(lens - K - 1, 0).sum())
+
+    with kcount.KmerCounter(K, expected_instances=expect_inst) as kc:
+        kc.add_reads(rb, ro)
+        kc.finish()
+        st = kc.stats()
+        a = _sorted_table(*kc.survivors(sort=False))
+    assert st["instances_parsed"] == expect_inst == st["instances_inserted"]
+    assert st["dropped"] == 0 and st["table_retries"] == 0
+    assert st["survivors"] == len(a[0]) and st["distinct"] == st["survivors"] + st["purged"]
+    keys, counts, left, right = a
+    assert np.all(keys[1:] != keys[:-1]), "a k-mer appears twice in the table"
+    assert counts.min() >= 2, "depth filter (kcount_cpu.cpp:497)"
+    for ext in (left, right):
+        assert np.isin(ext, np.frombuffer(b"ACGTFX", dtype=np.uint8)).all()
+    assert not np.any((left == ord("X")) & (right == ord("X"))), "X/X k-mers are purged (kcount_cpu.cpp:519)"
+    assert np.all(keys <= _revcomp21(keys)), "k-mers are canonical (kcount_cpu.cpp:326-331)"
+    assert np.all(keys & np.uint64((1 << (64 - 2 * K)) - 1) == 0), "bits past k are zero (kmer.hpp:61-75)"
+
+    # other batching, explicit partition count, reads resident in HBM: same table
+    with kcount.ResidentReads(rb, ro, batch_reads=3_000_000) as rr, kcount.KmerCounter(K, num_partitions=50_000) as kc:
+        kc.add_reads_resident(rr)
+        kc.finish()
+        b = _sorted_table(*kc.survivors(sort=False))
+    for x, y, what in zip(a, b, ("k-mers", "counts", "left", "right")):
+        assert np.array_equal(x, y), f"{what} depend on batching / partitioning"
+
+    # two shards (quick_hash(minimizer) % 2, kmer_dht.cpp:192-196), each parsing half of the reads: disjoint, union == table
+    n = len(ro) - 1
+    half = n // 2
+    shards = [kcount.KmerCounter(K, num_shards=2, shard_id=i, expected_instances=expect_inst // 2) for i in range(2)]
+    try:
+        for i, (r0, r1) in enumerate(((0, half), (half, n))):
+            shards[i].add_reads(rb[int(ro[r0]):int(ro[r1])], ro[r0:r1 + 1] - ro[r0])
+        kcount.finish_local_group(shards)
+        parts = [s.survivors(sort=False) for s in shards]
+    finally:
+        for s in shards:
+            s.close()
+    assert 0.45 < len(parts[0][1]) / len(keys) < 0.55, "shards are balanced"
+    c = _sorted_table(*[np.concatenate([p[j] for p in parts]) for j in range(4)])
+    for x, y, what in zip(a, c, ("k-mers", "counts", "left", "right")):
+        assert np.array_equal(x, y), f"{what} depend on sharding"
