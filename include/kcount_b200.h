@@ -107,6 +107,14 @@ int kc_reads_create(int32_t device, const uint8_t *bytes, const uint64_t *offset
                     kc_reads **out);
 int kc_add_reads_resident(kc_handle *h, kc_reads *reads);
 int kc_reads_destroy(kc_reads *reads);
+/* the step before the path: FASTQ text -> PackedRead bytes on the device, exactly PackedRead's constructor
+ * (packed_reads.cpp:73-109: A0 C1 G2 T3, N and IUPAC codes 4, quality min(q - qual_offset, 31) in the high 5 bits; any other
+ * character is the reference's DIE and comes back as KC_ERR_BADCHAR from the first kc_add_reads_resident /
+ * kc_reads_copy_packed). seqs and quals are the concatenated sequence and quality lines, offsets[n+1] as in kc_add_reads.
+ * The reads then never exist in packed form on the host unless kc_reads_copy_packed fetches them. */
+int kc_reads_create_fastq(int32_t device, const char *seqs, const char *quals, const uint64_t *offsets, uint64_t n_reads,
+                          int32_t qual_offset, int32_t batch_reads, kc_reads **out);
+int kc_reads_copy_packed(kc_reads *reads, uint8_t *bytes_out);
 /* add_ctg_kmers' loop -> process_seq(ctg.seq, ctg.get_uint16_t_depth()) (kcount.cpp:123-130, contigs.hpp:57-66).
  * seqs = ASCII ACGTN (host), offsets[n+1], depths = Contig::depth doubles. Any length; long contigs are tiled. */
 int kc_add_contigs(kc_handle *h, const char *seqs, const uint64_t *offsets, const double *depths, uint64_t n_ctgs);
@@ -141,6 +149,11 @@ int kc_finish_to_host(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char
 /* local_kmers of this shard (kmer_dht.hpp:119, dbjg_traversal.cpp:301): n rows of N_LONGS words, u16 count, left, right */
 int kc_num_survivors(kc_handle *h, uint64_t *n);
 int kc_copy_survivors(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char *left, char *right);
+/* KmerDHT::dump_kmers (kmer_dht.cpp:238-266, what --dump-kmers / analyze_kmers(..., dump_kmers=true) writes): one line per
+ * surviving k-mer, "KMER count left right"; a path ending in .gz is gzip-compressed like the reference's kmers-<k>.txt.gz.
+ * Line order is unspecified (the reference iterates a hash map). */
+int kc_dump_kmers(kc_handle *h, const char *path);
+
 /* device-resident view of the same arrays (valid until kc_destroy) */
 int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,
                         const char **d_right);

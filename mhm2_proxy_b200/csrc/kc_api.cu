@@ -701,8 +701,58 @@ struct kc_reads {
   std::vector<cudaEvent_t> ready;   // per batch: its bytes and offsets have arrived
   std::vector<u32> max_len;         // per batch
   std::vector<u64> h_offsets;       // kept only when some read is longer than one parse tile (host-side tiling needs them)
-  std::string err;
+  u32 *d_err = nullptr;             // kc_reads_create_fastq: set by the packing kernel on an illegal base character
+  bool err_checked = false;
+  void *stage[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // kc_reads_create_fastq: ASCII seq / qual staging, two slots
 };
+
+namespace {
+// FASTQ text -> PackedRead bytes (PackedRead::PackedRead, packed_reads.cpp:73-109): low 3 bits A0 C1 G2 T3, N and the IUPAC
+// codes 4; high 5 bits min(qual - qual_offset, 31) with the reference's unsigned-char wrap for negative differences.
+// Anything else is the reference's DIE("Illegal char"): reported through *err. 16 bases per thread, 128-bit accesses.
+__device__ __forceinline__ u32 pack_base(u32 c, u32 q, int qual_offset, u32 *err) {
+  u32 code;
+  switch (c) {
+    case 'A': code = 0; break;
+    case 'C': code = 1; break;
+    case 'G': code = 2; break;
+    case 'T': code = 3; break;
+    case 'N': case 'U': case 'R': case 'Y': case 'K': case 'M': case 'S': case 'W': case 'B': case 'D': case 'H': case 'V': code = 4; break;
+    default: code = 4; *err = 1; break;
+  }
+  int d = (int)(signed char)q - qual_offset;  // `char` is signed on the reference's platforms
+  if (d > 31) d = 31;
+  return (code | (((u32)(unsigned char)d) << 3)) & 0xFFu;
+}
+
+// seq, qual and out must be congruent modulo 16 (the staging copy is placed accordingly): a byte-wise head up to the first
+// 16-byte boundary, 128-bit body, byte-wise tail
+__global__ void __launch_bounds__(256) pack_reads_kernel(const uint8_t *seq, const uint8_t *qual, u64 n, int qual_offset, uint8_t *out,
+                                                         u32 *err) {
+  const u64 head = min(n, (u64)((16 - ((size_t)out & 15)) & 15));
+  const u64 nvec = (n - head) / 16, tail0 = head + nvec * 16;
+  const uint4 *s16 = (const uint4 *)(seq + head), *q16 = (const uint4 *)(qual + head);
+  uint4 *o16 = (uint4 *)(out + head);
+  for (u64 v = (u64)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (u64)gridDim.x * blockDim.x) {
+    const uint4 s4 = s16[v], q4 = q16[v];
+    const u32 sw[4] = {s4.x, s4.y, s4.z, s4.w}, qw[4] = {q4.x, q4.y, q4.z, q4.w};
+    u32 ow[4];
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+      u32 o = 0;
+#pragma unroll
+      for (int b = 0; b < 4; b++) o |= pack_base((sw[w] >> (8 * b)) & 0xFFu, (qw[w] >> (8 * b)) & 0xFFu, qual_offset, err) << (8 * b);
+      ow[w] = o;
+    }
+    o16[v] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < head) out[threadIdx.x] = (uint8_t)pack_base(seq[threadIdx.x], qual[threadIdx.x], qual_offset, err);
+    const u64 i = tail0 + threadIdx.x;
+    if (threadIdx.x < 16 && i < n) out[i] = (uint8_t)pack_base(seq[i], qual[i], qual_offset, err);
+  }
+}
+}  // namespace
 
 extern "C" int kc_reads_create(int32_t device, const uint8_t *bytes, const uint64_t *offsets, uint64_t n_reads, int32_t batch_reads,
                                kc_reads **out) {
@@ -752,9 +802,92 @@ extern "C" int kc_reads_destroy(kc_reads *r) {
   for (auto e : r->ready) cudaEventDestroy(e);
   dev_free(r->d_bytes);
   dev_free(r->d_offsets);
+  dev_free(r->d_err);
+  for (int sl = 0; sl < 2; sl++)
+    for (int j = 0; j < 2; j++) dev_free(r->stage[sl][j]);
   if (r->stream) cudaStreamDestroy(r->stream);
   delete r;
   return KC_OK;
+}
+
+extern "C" int kc_reads_create_fastq(int32_t device, const char *seqs, const char *quals, const uint64_t *offsets, uint64_t n_reads,
+                                     int32_t qual_offset, int32_t batch_reads, kc_reads **out) {
+  if (!out) return KC_ERR_INVALID;
+  *out = nullptr;
+  if (!seqs || !quals || !offsets || offsets[0] != 0) return KC_ERR_INVALID;
+  kc_handle *h = nullptr;
+  kc_reads *r = new kc_reads();
+  *out = r;
+  r->device = device;
+  r->n_reads = n_reads;
+  r->total_bytes = offsets[n_reads];
+  CK(cudaSetDevice(device));
+  CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+  CK(dev_alloc((void **)&r->d_bytes, r->total_bytes + 64));
+  CK(dev_alloc((void **)&r->d_offsets, (n_reads + 1) * 8));
+  CK(dev_alloc((void **)&r->d_err, 64));
+  CK(cudaMemsetAsync(r->d_err, 0, 64, r->stream));
+  u64 batch = batch_reads > 0 ? (u64)batch_reads : (2ull << 20);
+  const u64 avg = std::max<u64>(1, r->total_bytes / std::max<u64>(n_reads, 1));
+  batch = std::max<u64>(1, std::min<u64>(batch, (1ull << 30) / avg));
+  r->batch = batch;
+  const u64 nb = (n_reads + batch - 1) / batch;
+  u64 slot_bytes = 0;
+  for (u64 bi = 0; bi < nb; bi++) {
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    slot_bytes = std::max<u64>(slot_bytes, offsets[r1] - offsets[r0]);
+  }
+  for (int sl = 0; sl < 2; sl++)
+    for (int j = 0; j < 2; j++) CK(dev_alloc(&r->stage[sl][j], slot_bytes + 64));
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  bool any_long = false;
+  for (u64 bi = 0; bi < nb; bi++) {  // one stream: copy, copy, pack: slot reuse is ordered by the stream itself
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    const u64 b0 = offsets[r0], nbytes = offsets[r1] - b0;
+    const int sl = (int)(bi & 1);
+    // the text is staged at the same offset modulo 16 as its destination, so that the kernel's 128-bit body is aligned on
+    // both sides
+    const u64 mis = b0 & 15;
+    uint8_t *st_s = (uint8_t *)r->stage[sl][0] + mis, *st_q = (uint8_t *)r->stage[sl][1] + mis;
+    CK(cudaMemcpyAsync(st_s, seqs + b0, nbytes, cudaMemcpyHostToDevice, r->stream));
+    CK(cudaMemcpyAsync(st_q, quals + b0, nbytes, cudaMemcpyHostToDevice, r->stream));
+    CK(cudaMemcpyAsync(r->d_offsets + r0, offsets + r0, (r1 - r0 + 1) * 8, cudaMemcpyHostToDevice, r->stream));
+    if (nbytes) pack_reads_kernel<<<sms * 8, 256, 0, r->stream>>>(st_s, st_q, nbytes, qual_offset, r->d_bytes + b0, r->d_err);
+    cudaEvent_t e;
+    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(cudaEventRecord(e, r->stream));
+    r->ready.push_back(e);
+  }
+  CK(cudaGetLastError());
+  for (u64 bi = 0; bi < nb; bi++) {
+    const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
+    u64 ml = 0;
+    for (u64 i = r0; i < r1; i++) ml = std::max<u64>(ml, offsets[i + 1] - offsets[i]);
+    r->max_len.push_back((u32)std::min<u64>(ml, 0xFFFFFFFFu));
+    any_long = any_long || ml > (u64)SEG_MAX;
+  }
+  if (any_long) r->h_offsets.assign(offsets, offsets + n_reads + 1);
+  return KC_OK;
+}
+
+namespace {
+int reads_check(kc_reads *r) {  // the packing kernel's verdict (waits for the upload)
+  if (!r->d_err || r->err_checked) return KC_OK;
+  u32 e = 0;
+  if (cudaStreamSynchronize(r->stream) != cudaSuccess) return KC_ERR_CUDA;
+  if (cudaMemcpy(&e, r->d_err, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return KC_ERR_CUDA;
+  r->err_checked = true;
+  return e ? KC_ERR_BADCHAR : KC_OK;
+}
+}  // namespace
+
+extern "C" int kc_reads_copy_packed(kc_reads *r, uint8_t *bytes_out) {
+  if (!r || !bytes_out) return KC_ERR_INVALID;
+  if (cudaSetDevice(r->device) != cudaSuccess) return KC_ERR_CUDA;
+  if (cudaStreamSynchronize(r->stream) != cudaSuccess) return KC_ERR_CUDA;
+  if (cudaMemcpy(bytes_out, r->d_bytes, r->total_bytes, cudaMemcpyDeviceToHost) != cudaSuccess) return KC_ERR_CUDA;
+  return reads_check(r);
 }
 
 extern "C" int kc_add_reads_resident(kc_handle *h, kc_reads *r) {
@@ -783,6 +916,7 @@ extern "C" int kc_add_reads_resident(kc_handle *h, kc_reads *r) {
   }
   h->st.num_seqs += r->n_reads;
   h->st.num_bases += r->total_bytes;
+  if (int rcx = reads_check(r)) return fail(h, rcx, "kc_reads_create_fastq: illegal base character in the reads (packed_reads.cpp:104)");
   return KC_OK;
 }
 
@@ -1305,6 +1439,78 @@ extern "C" int kc_copy_survivors(kc_handle *h, uint64_t *kmer_words, uint16_t *c
   if (right) CK(cudaMemcpyAsync(right, h->out_right.p, n, cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
   return KC_OK;
+}
+
+// KmerDHT::dump_kmers (kmer_dht.cpp:238-266): one line per surviving k-mer, "KMER count left right". The reference writes
+// kmers-<k>.txt.gz per rank through zstr; here the caller names the file, ".gz" selects gzip (libz is loaded on demand), and
+// the order of lines is unspecified, as it is in the reference (hash-map iteration order).
+extern "C" int kc_dump_kmers(kc_handle *h, const char *path) {
+  if (!h || !path) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  CK(cudaSetDevice(h->cfg.device));
+  const u64 n = h->n_surv;
+  const int KW = h->KW, k = h->cfg.kmer_len;
+  const size_t plen = strlen(path);
+  const bool gz = plen > 3 && strcmp(path + plen - 3, ".gz") == 0;
+  void *zlib = nullptr;
+  void *(*zopen)(const char *, const char *) = nullptr;
+  int (*zwrite)(void *, const void *, unsigned) = nullptr;
+  int (*zclose)(void *) = nullptr;
+  void *zf = nullptr;
+  FILE *f = nullptr;
+  if (gz) {
+    zlib = dlopen("libz.so.1", RTLD_NOW);
+    if (!zlib) zlib = dlopen("libz.so", RTLD_NOW);
+    if (!zlib) return fail(h, KC_ERR_INVALID, "%s: libz is not available, use a name without .gz", path);
+    *(void **)(&zopen) = dlsym(zlib, "gzopen");
+    *(void **)(&zwrite) = dlsym(zlib, "gzwrite");
+    *(void **)(&zclose) = dlsym(zlib, "gzclose");
+    if (!zopen || !zwrite || !zclose) return fail(h, KC_ERR_INVALID, "libz lacks gzopen/gzwrite/gzclose");
+    zf = zopen(path, "wb1");
+    if (!zf) return fail(h, KC_ERR_INVALID, "cannot open %s", path);
+  } else {
+    f = fopen(path, "wb");
+    if (!f) return fail(h, KC_ERR_INVALID, "cannot open %s", path);
+  }
+  const u64 CH = 1u << 20;  // entries per round trip
+  std::vector<u64> keys(std::min(n, CH) * KW);
+  std::vector<uint16_t> counts(std::min(n, CH));
+  std::vector<char> left(std::min(n, CH)), right(std::min(n, CH));
+  std::string buf;
+  int rc = KC_OK;
+  for (u64 c0 = 0; c0 < n && rc == KC_OK; c0 += CH) {
+    const u64 m = std::min(CH, n - c0);
+    CK(cudaMemcpy(keys.data(), (const u64 *)h->out_keys.p + c0 * KW, m * KW * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(counts.data(), (const uint16_t *)h->out_counts.p + c0, m * 2, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(left.data(), (const char *)h->out_left.p + c0, m, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(right.data(), (const char *)h->out_right.p + c0, m, cudaMemcpyDeviceToHost));
+    buf.clear();
+    buf.reserve(m * (k + 12));
+    char num[16];
+    for (u64 i = 0; i < m; i++) {
+      for (int b = 0; b < k; b++) buf.push_back("ACGT"[(keys[i * KW + (b >> 5)] >> (2 * (31 - (b & 31)))) & 3]);  // kmer.cpp:322-343
+      const int nl = snprintf(num, sizeof(num), " %u ", (unsigned)counts[i]);
+      buf.append(num, nl);
+      buf.push_back(left[i]);
+      buf.push_back(' ');
+      buf.push_back(right[i]);
+      buf.push_back('\n');
+    }
+    if (gz) {
+      for (size_t o = 0; o < buf.size() && rc == KC_OK; o += (1u << 30)) {
+        const unsigned len = (unsigned)std::min<size_t>(buf.size() - o, 1u << 30);
+        if (zwrite(zf, buf.data() + o, len) != (int)len) rc = fail(h, KC_ERR_INVALID, "write to %s failed", path);
+      }
+    } else if (fwrite(buf.data(), 1, buf.size(), f) != buf.size()) {
+      rc = fail(h, KC_ERR_INVALID, "write to %s failed", path);
+    }
+  }
+  if (gz) {
+    if (zclose(zf) != 0 && rc == KC_OK) rc = fail(h, KC_ERR_INVALID, "closing %s failed", path);
+  } else if (fclose(f) != 0 && rc == KC_OK) {
+    rc = fail(h, KC_ERR_INVALID, "closing %s failed", path);
+  }
+  return rc;
 }
 
 extern "C" int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,

@@ -36,7 +36,7 @@ class KcStats(C.Structure):
 
 
 EXPORTS = [
-    "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_reads_create", "kc_add_reads_resident", "kc_reads_destroy", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
+    "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_reads_create", "kc_reads_create_fastq", "kc_reads_copy_packed", "kc_add_reads_resident", "kc_reads_destroy", "kc_dump_kmers", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
     "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_to_host", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
 ]
@@ -70,6 +70,9 @@ def load_library():
     lib.kc_finish.argtypes = [vp]
     lib.kc_reads_create.argtypes = [i32, vp, vp, u64, i32, C.POINTER(vp)]
     lib.kc_add_reads_resident.argtypes = [vp, vp]
+    lib.kc_reads_create_fastq.argtypes = [i32, vp, vp, vp, u64, i32, i32, C.POINTER(vp)]
+    lib.kc_reads_copy_packed.argtypes = [vp, vp]
+    lib.kc_dump_kmers.argtypes = [vp, C.c_char_p]
     lib.kc_reads_destroy.argtypes = [vp]
     lib.kc_finish_to_host.argtypes = [vp, vp, vp, vp, vp, u64, C.POINTER(u64)]
     lib.kc_finish_local_group.argtypes = [C.POINTER(vp), i32]
@@ -168,6 +171,10 @@ class KmerCounter:
     def finish(self):
         self._ck(self.lib.kc_finish(self.h), "kc_finish")
 
+    def dump_kmers(self, path):
+        """KmerDHT::dump_kmers: "KMER count left right" per surviving k-mer; .gz -> gzip."""
+        self._ck(self.lib.kc_dump_kmers(self.h, str(path).encode()), "kc_dump_kmers")
+
     def add_reads_resident(self, reads):
         """Parse reads that a ResidentReads object holds (or is still uploading) in HBM."""
         self._ck(self.lib.kc_add_reads_resident(self.h, reads.r), "kc_add_reads_resident")
@@ -262,6 +269,31 @@ class ResidentReads:
         if rc != KC_OK:
             self.close()
             raise KcountError(f"kc_reads_create failed ({ERR_NAMES.get(rc, rc)})")
+
+    @classmethod
+    def from_fastq(cls, seqs, quals, offsets, qual_offset=33, device=0, batch_reads=0):
+        """kc_reads_create_fastq: concatenated sequence and quality lines (uint8 arrays) are packed into PackedRead bytes on
+        the device."""
+        self = cls.__new__(cls)
+        self.lib = load_library()
+        self._keep = (np.ascontiguousarray(seqs, dtype=np.uint8), np.ascontiguousarray(quals, dtype=np.uint8),
+                      np.ascontiguousarray(offsets, dtype=np.uint64))
+        self.total = int(self._keep[2][-1])
+        self.r = C.c_void_p()
+        rc = self.lib.kc_reads_create_fastq(device, _ptr(self._keep[0]), _ptr(self._keep[1]), _ptr(self._keep[2]),
+                                            len(self._keep[2]) - 1, qual_offset, batch_reads, C.byref(self.r))
+        if rc != KC_OK:
+            self.close()
+            raise KcountError(f"kc_reads_create_fastq failed ({ERR_NAMES.get(rc, rc)})")
+        return self
+
+    def packed(self):
+        """The PackedRead bytes as they sit in HBM (kc_reads_copy_packed)."""
+        out = np.empty(int(self._keep[-1][-1]), dtype=np.uint8)
+        rc = self.lib.kc_reads_copy_packed(self.r, _ptr(out))
+        if rc != KC_OK:
+            raise KcountError(f"kc_reads_copy_packed failed ({ERR_NAMES.get(rc, rc)})")
+        return out
 
     def close(self):
         if self.r:

@@ -251,6 +251,75 @@ def test_reads_ascii_equals_packed(built, community):
     _assert_same(got, _oracle(k, rb, ro), "ascii reads")
 
 
+def _pack_like_reference(seq, qual, qual_offset):
+    """numpy restatement of PackedRead::PackedRead (packed_reads.cpp:73-109): A0 C1 G2 T3, N + IUPAC 4;
+    bytes[i] |= (unsigned char)min(quals[i] - qual_offset, 31) << 3, truncated to the byte"""
+    code = np.full(256, 255, dtype=np.uint8)
+    for ch, c in zip(b"ACGT", range(4)):
+        code[ch] = c
+    for ch in b"NURYKMSWBDHV":
+        code[ch] = 4
+    c = code[seq]
+    assert (c != 255).all()
+    d = np.minimum(qual.astype(np.int64) - qual_offset, 31)
+    return (c | (((d & 0xFF) << 3) & 0xFF)).astype(np.uint8)
+
+
+def test_fastq_text_is_packed_on_the_device(built, community):
+    """kc_reads_create_fastq == PackedRead's constructor byte for byte (incl. IUPAC codes, quality clamp at 31 and the
+    unsigned-char wrap below the offset), at ragged batch boundaries; the table from it == the table from packed input;
+    an illegal character is reported (the reference DIEs)."""
+    from mhm2_proxy_b200 import kcount
+    k = 31
+    rb, ro = synth.make_reads(5000, community, error_rate=0.01, seed=21, n_rate=2e-3, var_len=True)
+    rng = np.random.default_rng(3)
+    iupac = np.frombuffer(b"NURYKMSWBDHV", dtype=np.uint8)
+    seq = np.frombuffer(b"ACGTN", dtype=np.uint8)[rb & 7].copy()
+    isn = (rb & 7) == 4
+    seq[isn] = iupac[rng.integers(0, len(iupac), int(isn.sum()))]
+    qual = ((rb >> 3).astype(np.int64) + 33)
+    odd = rng.random(len(rb)) < 0.01  # qualities outside 0..31 after the offset
+    qual[odd] = rng.integers(33 - 3, 33 + 60, int(odd.sum()))
+    qual = qual.astype(np.uint8)
+    want = _pack_like_reference(seq, qual, 33)
+    with kcount.ResidentReads.from_fastq(seq, qual, ro, qual_offset=33, batch_reads=777) as rr:
+        got = rr.packed()
+        assert np.array_equal(got, want)
+        with kcount.KmerCounter(k, num_partitions=6) as kc:
+            kc.add_reads_resident(rr)
+            kc.finish()
+            _assert_same(kc.survivors(), _oracle(k, want, ro), "reads packed on the device")
+    bad = seq.copy()
+    bad[len(bad) // 2] = ord("x")
+    with kcount.ResidentReads.from_fastq(bad, qual, ro, qual_offset=33) as rr, kcount.KmerCounter(k, num_partitions=6) as kc:
+        with pytest.raises(kcount.KcountError, match="BADCHAR"):
+            kc.add_reads_resident(rr)
+
+
+def test_dump_kmers_matches_reference_format(built, community, tmp_path):
+    """kc_dump_kmers writes what KmerDHT::dump_kmers writes (kmer_dht.cpp:238-266): "KMER count left right" per survivor,
+    gzip when the name ends in .gz; compared as a set of lines with the oracle's table."""
+    import gzip
+    from mhm2_proxy_b200 import kcount
+    for k in (21, 55):
+        rb, ro = synth.make_reads(3000, community, error_rate=0.01, seed=50 + k)
+        ref = _oracle(k, rb, ro)
+        want = set()
+        for row, c, le, ri in zip(ref.keys, ref.counts, ref.left, ref.right):
+            kmer = "".join("ACGT"[(int(row[b >> 5]) >> (2 * (31 - (b & 31)))) & 3] for b in range(k))
+            want.add(f"{kmer} {int(c)} {chr(le)} {chr(ri)}")
+        with kcount.KmerCounter(k, num_partitions=3) as kc:
+            kc.add_reads(rb, ro)
+            kc.finish()
+            kc.dump_kmers(tmp_path / f"kmers-{k}.txt.gz")
+            kc.dump_kmers(tmp_path / f"kmers-{k}.txt")
+        with gzip.open(tmp_path / f"kmers-{k}.txt.gz", "rt") as f:
+            got_gz = f.read().splitlines()
+        got = (tmp_path / f"kmers-{k}.txt").read_text().splitlines()
+        assert len(got) == len(want) == len(got_gz)
+        assert set(got) == want and set(got_gz) == want
+
+
 def test_resident_reads_shared_by_rounds(built, community):
     """kc_reads_create uploads the PackedRead bytes once; two k rounds (and a round with long, tiled reads) parse them from
     HBM and give the tables kc_add_reads gives."""
