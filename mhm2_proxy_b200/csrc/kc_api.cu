@@ -75,6 +75,7 @@ struct kc_handle {
   std::vector<Block> rblocks;      // received from peers (multi-shard)
   DevBuf stage_bytes[2], stage_offs[2];
   DevBuf d_cursor, d_misc;  // d_misc: u64 instances, u32 err
+  DevBuf d_elist, d_ecnt;   // supermer lists of the batch being parsed (parse_kernel -> fill_kernel)
   // outputs
   DevBuf out_keys, out_counts, out_left, out_right, pf_keys, pf_vals;
   u64 n_surv = 0, n_pf = 0;
@@ -409,7 +410,7 @@ __global__ void __launch_bounds__(1024) scan_tile_offsets_kernel(u64 *tile_sum, 
 }
 
 __global__ void __launch_bounds__(1024) scan_apply_kernel(const BucketHist *hist, u32 n, const u64 *tile_off, u64 *base, u32 P,
-                                                          u64 *totals) {
+                                                          u64 *totals, u32 *cursor) {
   __shared__ u64 wt[33];
   const u32 i0 = blockIdx.x * SCAN_TILE + threadIdx.x * 4;
   u32 c[4];
@@ -426,6 +427,7 @@ __global__ void __launch_bounds__(1024) scan_apply_kernel(const BucketHist *hist
     const u32 i = i0 + j;
     if (i < n) {
       base[i] = run;
+      if (cursor) cursor[i] = (u32)run;  // the fill kernel's bucket cursors start at the bucket's first record
       if (totals && i % P == 0) totals[i / P] = run;
     }
     run += c[j];
@@ -438,12 +440,13 @@ __global__ void __launch_bounds__(1024) scan_apply_kernel(const BucketHist *hist
 }
 
 // base must hold n + 1 entries, tile_scratch (n + SCAN_TILE - 1) / SCAN_TILE + 1
-int bucket_scan(kc_handle *h, const BucketHist *hist, u32 n, u64 *base, u32 P, u64 *totals, u64 *tile_scratch, cudaStream_t st) {
+int bucket_scan(kc_handle *h, const BucketHist *hist, u32 n, u64 *base, u32 P, u64 *totals, u64 *tile_scratch, cudaStream_t st,
+                u32 *cursor = nullptr) {
   const u32 ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
   if (ntiles > 1024) return KC_ERR_INVALID;
   scan_tile_sums_kernel<<<ntiles, 1024, 0, st>>>(hist, n, tile_scratch);
   scan_tile_offsets_kernel<<<1, 1024, 0, st>>>(tile_scratch, ntiles);
-  scan_apply_kernel<<<ntiles, 1024, 0, st>>>(hist, n, tile_scratch, base, P, totals);
+  scan_apply_kernel<<<ntiles, 1024, 0, st>>>(hist, n, tile_scratch, base, P, totals, cursor);
   h->st.gpu_launches += 3;
   return cudaGetLastError() == cudaSuccess ? KC_OK : KC_ERR_CUDA;
 }
@@ -455,7 +458,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   if (nseq == 0) return KC_OK;
   const u32 NP = h->P * (u32)h->cfg.num_shards;
   const int N = h->cfg.num_shards;
-  RC(ensure(h, h->d_cursor, sizeof(BucketHist) * NP));
+  RC(ensure(h, h->d_cursor, sizeof(u32) * NP));
   RC(ensure(h, h->d_tot, sizeof(u64) * (size_t)(N + 1)));
   ParseArgs a;
   memset(&a, 0, sizeof(a));
@@ -486,15 +489,26 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   int threads = 128;
   while (threads > 32 && (size_t)threads * words_per_thread * 4 > 96u * 1024u) threads >>= 1;
   const size_t smem = (size_t)threads * words_per_thread * 4;
-  void (*k_count)(const ParseArgs) = threads == 128 ? parse_kernel<false, 128> : threads == 64 ? parse_kernel<false, 64> : parse_kernel<false, 32>;
-  void (*k_fill)(const ParseArgs) = threads == 128 ? parse_kernel<true, 128> : threads == 64 ? parse_kernel<true, 64> : parse_kernel<true, 32>;
+  const size_t smem_fill = (size_t)threads * (a.nsb + a.nsv) * 4;  // the fill kernel keeps only the packed sequence
+  void (*k_count)(const ParseArgs) = threads == 128 ? parse_kernel<128> : threads == 64 ? parse_kernel<64> : parse_kernel<32>;
+  void (*k_fill)(const ParseArgs) = threads == 128 ? fill_kernel<128> : threads == 64 ? fill_kernel<64> : fill_kernel<32>;
   CK(cudaFuncSetAttribute(k_count, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  CK(cudaFuncSetAttribute(k_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_fill, threads, smem));
+  CK(cudaFuncSetAttribute(k_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_fill));
+  int per_sm = 1, per_sm_fill = 1;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_count, threads, smem));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_fill, k_fill, threads, smem_fill));
   per_sm = std::max(per_sm, 1);
+  per_sm_fill = std::max(per_sm_fill, 1);
   const u64 need_blocks = (nseq + threads - 1) / threads;
   const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * per_sm * 2);
+  const unsigned grid_fill = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * per_sm_fill * 2);
+  // supermer lists handed from the parse kernel to the fill kernel: one u32 per supermer, ecap slots per sequence
+  if (NP >= (1u << 24)) return fail(h, KC_ERR_INVALID, "internal: %u buckets do not fit the 24-bit list entries", NP);
+  a.ecap = std::max(1, max_len - a.k - 1);
+  RC(ensure(h, h->d_elist, need_blocks * (size_t)threads * (size_t)a.ecap * 4));
+  RC(ensure(h, h->d_ecnt, nseq));
+  a.elist = (u32 *)h->d_elist.p;
+  a.ecnt = (uint8_t *)h->d_ecnt.p;
 
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
@@ -512,7 +526,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   // bucket layout on the device: the host only needs the totals (allocation size, the range that goes to each shard)
   CK(dev_alloc((void **)&blk.d_base, sizeof(u64) * ((size_t)NP + 1)));
   RC(ensure(h, h->d_scan, sizeof(u64) * 1032));
-  RC(bucket_scan(h, blk.d_hist, NP, blk.d_base, h->P, (u64 *)h->d_tot.p, (u64 *)h->d_scan.p, h->s_main));
+  RC(bucket_scan(h, blk.d_hist, NP, blk.d_base, h->P, (u64 *)h->d_tot.p, (u64 *)h->d_scan.p, h->s_main, (u32 *)h->d_cursor.p));
   CK(cudaMemcpyAsync(h->h_pin, h->d_tot.p, sizeof(u64) * (size_t)(N + 1), cudaMemcpyDeviceToHost, h->s_main));
   CK(cudaStreamSynchronize(h->s_main));
   blk.dest_base.assign(h->h_pin, h->h_pin + N + 1);
@@ -526,13 +540,12 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   }
   const size_t rec_bytes = (size_t)hs * a.rw * 4;
   CK(dev_alloc((void **)&blk.rec, rec_bytes + 64));
-  CK(cudaMemsetAsync(h->d_cursor.p, 0, sizeof(BucketHist) * NP, h->s_main));
+  if (hs >> 32) return fail(h, KC_ERR_INVALID, "internal: %llu supermers in one batch do not fit the 32-bit bucket cursors", (unsigned long long)hs);
   // FILL
-  a.hist = (BucketHist *)h->d_cursor.p;
-  a.base = blk.d_base;
+  a.cursor = (u32 *)h->d_cursor.p;
   a.rec = blk.rec;
   CK(cudaEventRecord(h->ev_d, h->s_main));
-  k_fill<<<grid, threads, smem, h->s_main>>>(a);
+  k_fill<<<grid_fill, threads, smem_fill, h->s_main>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
@@ -1579,7 +1592,7 @@ extern "C" int kc_destroy(kc_handle *h) {
   if (h->s_comm) cudaStreamSynchronize(h->s_comm);
   for (auto &b : h->blocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   for (auto &b : h->rblocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
-  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_cursor, &h->d_meta, &h->d_meta_all,
+  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_cursor, &h->d_elist, &h->d_ecnt, &h->d_meta, &h->d_meta_all,
                     &h->d_tot, &h->d_scan, &h->d_scan_comm, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
                     &h->pf_keys, &h->pf_vals};
   for (DevBuf *b : bufs) release(*b);

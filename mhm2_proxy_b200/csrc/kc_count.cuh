@@ -118,9 +118,8 @@ __device__ __forceinline__ bool group_barrier_or(int g, bool pred) {
       : "memory");
   return r != 0;
 }
-__device__ __forceinline__ uint4 lds128_volatile(const void *p) {
+__device__ __forceinline__ uint4 lds128_volatile(u32 a) {  // a: shared-space address (converted once per kernel)
   uint4 v;
-  const u32 a = (u32)__cvta_generic_to_shared(p);
   asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
   return v;
 }
@@ -150,9 +149,12 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   u32 *stage = stage_all + grp * (GRP_STAGE_WORDS + 4);
   uint16_t *expl = expl_all + grp * GRP_EXP;
   const int k = a.k, rw = a.rw;
-  const int nw = (k + 31) >> 5;
+  const int nw = KW == 1 ? 1 : (k + 31) >> 5;  // words of the key that hold bases: KW, or KW - 1 when k % 32 == 0
   const u64 last_mask = (k & 31) ? (~0ULL << (64 - 2 * (k & 31))) : ~0ULL;
+  const int rsh = 62 - 2 * (k & 31);  // where the base after the k-mer sits in the k-mer's last word (k % 32 != 0)
   const u32 nbuckets = a.tab_size >> 2;
+  const u32 tab_s = (u32)__cvta_generic_to_shared(tab);
+  const int nwb = a.nwb;
   const int sup_per_chunk = min(GRP_THREADS, GRP_STAGE_WORDS / rw);
   u32 my_max_probe = 0;
   // Work items are dealt round-robin to the CTAs: first the heavy list (outlier partitions, heaviest first, so that none of
@@ -266,17 +268,37 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           const u32 si = e & 255u;
           const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
           const u32 *rec = stage + si * rw;
-          const u32 hdr = rec[0];
+          const u32 hdr = CTG ? rec[0] : 0u;
           const u32 *p = rec + 1;
-          const u32 *pv = p + a.nwb;
+          const u32 *pv = p + nwb;
+          // words idx-1 .. idx+2*nw of the base stream hold the base before the k-mer, the k-mer and (k % 32 != 0) the base
+          // after it: one pass of funnel shifts yields all three (p[-1] is the header word, read but never selected)
+          const u32 *pw = p + (j >> 4);
+          const u32 sh = (u32)(j & 15) * 2u;
+          u32 wv[2 * KW + 2];
+#pragma unroll
+          for (int i = 0; i < 2 * KW + 2; i++) wv[i] = (i <= 2 * nw + 1) ? pw[i - 1] : 0u;
           u64 fwd[KW], rc[KW];
 #pragma unroll
-          for (int i = 0; i < KW; i++) fwd[i] = (i < nw) ? fetch64(p, j + 32 * i) : 0ULL;
-          // word nw - 1 keeps only its k % 32 bases; nw is KW or KW - 1 (static indices: no local memory)
+          for (int i = 0; i < KW; i++)
+            fwd[i] = ((u64)__funnelshift_l(wv[2 * i + 2], wv[2 * i + 1], sh) << 32) | __funnelshift_l(wv[2 * i + 3], wv[2 * i + 2], sh);
+          const int lcode = (int)(__funnelshift_l(wv[1], wv[0], sh) & 3u);
+          // word nw - 1 keeps only its k % 32 bases; nw is KW or KW - 1 (static indices: no local memory). Before the mask
+          // the same word still holds the base that follows the k-mer.
+          const u64 lastw = (nw == KW) ? fwd[KW - 1] : fwd[KW >= 2 ? KW - 2 : 0];
+          const int rcode = (k & 31) ? (int)((u32)(lastw >> rsh) & 3u) : fetch_base(p, j + k);
           if (nw == KW) fwd[KW - 1] &= last_mask;
-          else if (KW >= 2) fwd[KW >= 2 ? KW - 2 : 0] &= last_mask;
-          const int lcode = fetch_base(p, j - 1), lval = fetch_bit(pv, j - 1);
-          const int rcode = fetch_base(p, j + k), rval = fetch_bit(pv, j + k);
+          else if (KW >= 2) { fwd[KW >= 2 ? KW - 2 : 0] &= last_mask; fwd[KW - 1] = 0ULL; }
+          int lval, rval;
+          if (k <= 30) {  // both extension-valid bits sit in one 32-bit window of the bit stream
+            const int q = j - 1;
+            const u32 vw = __funnelshift_r(pv[q >> 5], pv[(q >> 5) + 1], (u32)q & 31u);
+            lval = (int)(vw & 1u);
+            rval = (int)((vw >> (k + 1)) & 1u);
+          } else {
+            lval = fetch_bit(pv, j - 1);
+            rval = fetch_bit(pv, j + k);
+          }
           revcomp_words<KW>(fwd, rc, k);
           int l, r;
           u64 key[KW];
@@ -290,7 +312,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             l = lval ? lcode : EXT_NONE;
             r = rval ? rcode : EXT_NONE;
           }
-          const u64 h = murmur64_words<KW>(key);  // Kmer::hash (kmer.cpp:465-468)
+          const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
           if (it.nsub > 1 && ((u32)(h >> 40) & (it.nsub - 1)) != it.sub) continue;
           // ---- find or claim: one 128-bit load per bucket, everything else on registers ----
           const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);  // never 0, so an empty entry never matches
@@ -298,11 +320,11 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           u32 mine = 0xFFFFFFFFu, idx = 0xFFFFFFFFu, probes = 0;
           bool claimed = false;
           for (;;) {
-            const uint4 bq = lds128_volatile(tab + 4 * bkt);
-            u32 mm = ((bq.x & ~IDX_MASK) == fp ? 1u : 0u) | ((bq.y & ~IDX_MASK) == fp ? 2u : 0u) |
-                     ((bq.z & ~IDX_MASK) == fp ? 4u : 0u) | ((bq.w & ~IDX_MASK) == fp ? 8u : 0u);
-            while (mm) {  // almost always exactly one candidate, and it is the key
-              const u32 en = (mm & 1u) ? bq.x : (mm & 2u) ? bq.y : (mm & 4u) ? bq.z : bq.w;
+            const uint4 bq = lds128_volatile(tab_s + 16u * bkt);
+            // an entry matches when its upper 19 bits equal the fingerprint (fp has bit 13 set: an empty entry never does)
+            const bool m0 = (bq.x ^ fp) <= IDX_MASK, m1 = (bq.y ^ fp) <= IDX_MASK, m2 = (bq.z ^ fp) <= IDX_MASK, m3 = (bq.w ^ fp) <= IDX_MASK;
+            if (m0 | m1 | m2 | m3) {  // almost always exactly one candidate, and it is the key
+              const u32 en = m0 ? bq.x : m1 ? bq.y : m2 ? bq.z : bq.w;
               const u32 cand = (en & IDX_MASK) - 1u;
               bool same = true;
 #pragma unroll
@@ -311,7 +333,23 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
                 idx = cand;
                 break;
               }
-              mm &= mm - 1u;
+              // rare (2^-18 per occupied entry): another key with our fingerprint came first; check the candidates after it
+              bool first = true;
+#pragma unroll
+              for (int q = 0; q < 4; q++) {
+                const u32 eq = q == 0 ? bq.x : q == 1 ? bq.y : q == 2 ? bq.z : bq.w;
+                if ((eq ^ fp) <= IDX_MASK && idx == 0xFFFFFFFFu) {
+                  if (first) {
+                    first = false;
+                  } else {
+                    const u32 c2 = (eq & IDX_MASK) - 1u;
+                    bool s2 = true;
+#pragma unroll
+                    for (int i = 0; i < KW; i++) s2 = s2 && (((volatile u64 *)keys)[(size_t)c2 * KW + i] == key[i]);
+                    if (s2) idx = c2;
+                  }
+                }
+              }
             }
             if (idx != 0xFFFFFFFFu) break;
             const u32 em = (bq.x == 0 ? 1u : 0u) | (bq.y == 0 ? 2u : 0u) | (bq.z == 0 ? 4u : 0u) | (bq.w == 0 ? 8u : 0u);
@@ -354,13 +392,15 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
               atomicAdd(v + l, 1u);
               if (r < 4) atomicAdd(v + 5 + r, 1u);
             } else {
-              const u32 shl = (u32)(l & 1) * 16u;
-              u32 old = atomicAdd(v + (l >> 1), 1u << shl);
-              if (((old >> shl) & 0xFFFFu) == 0xFFFFu) s_wide = 1;
+              // a half that was 0xFFFF before the add has wrapped (into its neighbour): the item is re-run with wide counters
+              const bool lodd = (l & 1) != 0;
+              u32 old = atomicAdd(v + (l >> 1), lodd ? 0x10000u : 1u);
+              if ((old | (lodd ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
               if (r < 4) {
-                const u32 hr = 5u + (u32)r, shr = (hr & 1u) * 16u;
-                old = atomicAdd(v + (hr >> 1), 1u << shr);
-                if (((old >> shr) & 0xFFFFu) == 0xFFFFu) s_wide = 1;
+                const u32 hr = 5u + (u32)r;
+                const bool rodd = (hr & 1u) != 0;
+                old = atomicAdd(v + (hr >> 1), rodd ? 0x10000u : 1u);
+                if ((old | (rodd ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
               }
             }
           } else {  // a contig instance: remembered as (occurrences, min depth, set of extension pairs), DESIGN.md "contig pass"

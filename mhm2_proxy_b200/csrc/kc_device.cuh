@@ -48,6 +48,28 @@ __host__ __device__ __forceinline__ u64 murmur64_words(const u64 *w) {
   return h1;
 }
 
+// Slot hash of the count stage's shared-memory table. Which slot a k-mer lands in is internal (SURVEY.md Appendix A.7:
+// slot hash, probing and capacity are free to differ from KmerMapExts::insert), so the table does not pay for the 45
+// instructions of MurmurHash3 per instance: two multiply / xor-fold rounds (9 instructions at KW = 1) spread the keys of
+// one partition — k-mers sharing a minimizer, many one substitution apart — as evenly as fmix64 does (tools/hash_quality.py).
+// murmur64_words stays the bit-exact Kmer::hash (KAT-tested through kc_prim_kmers).
+template <int KW>
+__host__ __device__ __forceinline__ u64 table_hash(const u64 *w) {
+  const u64 c = 0xD6E8FEB86659FD93ULL;
+  u64 h = w[0];
+#pragma unroll
+  for (int i = 1; i < KW; i++) {
+    h ^= h >> 32;
+    h = h * c ^ w[i];
+  }
+  h ^= h >> 32;
+  h *= c;
+  h ^= h >> 32;
+  h *= c;
+  h ^= h >> 32;
+  return h;
+}
+
 // hash_funcs.c:332-342
 __host__ __device__ __forceinline__ u64 quick_hash(u64 v) {
   v = v * 3935559000370003845ULL + 2691343689449507681ULL;

@@ -21,7 +21,9 @@
 //      words 1+nwb .. : "extension-valid" bits, LSB first      (nwv = ceil(nb_max / 32))
 // Only k-mers 1..len-k-1 of a sequence are counted (first and last never are, kcount_cpu.cpp:84-102); supermer
 // boundaries are free to differ from the reference's.
-// The kernel runs twice per batch: COUNT (bucket histogram only) then FILL (exact-size buckets, no overflow possible).
+// Two kernels per batch: parse_kernel (steps 1-2, bucket histogram, and the list of every sequence's supermers written
+// to HBM as one u32 per supermer: bucket | first k-mer << 24) -> bucket scan -> fill_kernel (step 1 again, then step 3 fed
+// from that list: no minimizer, no hash is computed twice) into exact-size buckets, no overflow possible.
 #pragma once
 #include "kc_device.cuh"
 
@@ -60,9 +62,12 @@ struct ParseArgs {
   u32 num_shards, num_parts;  // partitions per shard (any number >= 1)
   int nsb, nsv;            // shared words per thread for bases / valid bits
   int nwb, nwv, rw;        // record geometry
-  BucketHist *hist;        // COUNT: += ; FILL: running cursors (start at 0)
-  const u64 *base;         // FILL: index of the bucket's first record
-  u32 *rec;                // FILL: records
+  BucketHist *hist;        // parse: bucket histogram (+=)
+  u32 *cursor;             // fill: index of the next free record of every bucket (starts at the bucket's first record)
+  u32 *rec;                // fill: records
+  u32 *elist;              // supermer lists: entry e of the sequence handled by thread t of chunk c (= NT consecutive
+  int ecap;                //   sequences) at elist[((u64)c * ecap + e) * NT + t]; ecap = longest sequence - k - 1
+  uint8_t *ecnt;           // [nseq] entries in the list (a sequence of <= 256 bases has <= 254 supermers)
   u64 *instances;          // += number of k-mer instances parsed
   u32 *err;                // |= 1 on a contig character outside ACGTNacgtn
 };
@@ -121,8 +126,54 @@ __device__ __forceinline__ void decode16_ascii(const uint4 v, int lo, int hi, u3
   }
 }
 
-template <bool FILL, int NT>
-__global__ void __launch_bounds__(NT, (FILL ? 5 : 8) * 128 / NT) parse_kernel(const ParseArgs a) {
+// sequence s of the launch: where it starts, how long it is, its depth; false when it holds no counted k-mer
+__device__ __forceinline__ bool seq_header(const ParseArgs &a, u64 s, u64 &start, int &len, u32 &depth) {
+  if (s >= a.nseq) return false;
+  if (a.seg_start) {
+    start = a.seg_start[s];
+    len = (int)a.seg_len[s];
+    if (a.seg_depth) depth = a.seg_depth[s];
+  } else {
+    start = a.offsets[s];
+    len = (int)(a.offsets[s + 1] - start);
+  }
+  return len >= a.k + 2;  // kcount.cpp:79 (len < k) and: fewer than k+2 bases hold no counted k-mer
+}
+
+// ---- 1. load + pack: aligned 16-byte chunks; base q of the sequence sits at stream position a0 + q ----
+template <int NT>
+__device__ __forceinline__ int load_pack(const ParseArgs &a, const Strided<NT> sb, const Strided<NT> sv, u64 start, int len, bool &bad) {
+  const uint8_t *src = a.bytes + start;
+  const int a0 = (int)((uintptr_t)src & 15);
+  const uint4 *p16 = (const uint4 *)(src - a0);
+  const int end = a0 + len;
+  const int n16 = (end + 15) >> 4;
+  for (int c = 0; c < n16; c += 2) {
+    const uint4 v0 = __ldg(p16 + c);
+    const uint4 v1 = (c + 1 < n16) ? __ldg(p16 + c + 1) : make_uint4(0, 0, 0, 0);
+    u32 c0, b0, c1, b1;
+    if (a.ascii) {
+      decode16_ascii(v0, a0 - 16 * c, end - 16 * c, c0, b0, bad);
+      decode16_ascii(v1, a0 - 16 * (c + 1), (c + 1 < n16) ? end - 16 * (c + 1) : 0, c1, b1, bad);
+    } else {
+      decode16_packed(v0, a.qual_add, c0, b0);
+      decode16_packed(v1, a.qual_add, c1, b1);
+    }
+    sb.set(c, c0);
+    sb.set(c + 1, c1);
+    sv.set(c >> 1, b0 | (b1 << 16));
+  }
+  const int nwp = (n16 + 1) & ~1;
+  sb.set(nwp, 0);  // fetch64 may read 2 words past the last base
+  sb.set(nwp + 1, 0);
+  sb.set(nwp + 2, 0);
+  sv.set(nwp >> 1, 0);
+  sv.set((nwp >> 1) + 1, 0);
+  return a0;
+}
+
+template <int NT>
+__global__ void __launch_bounds__(NT, 8 * 128 / NT) parse_kernel(const ParseArgs a) {
   extern __shared__ __align__(16) u32 smem_parse[];
   const int t = threadIdx.x;
   const Strided<NT> sb{smem_parse + t};                                   // [nsb] 2-bit bases, 16 per word, MSB first
@@ -138,50 +189,13 @@ __global__ void __launch_bounds__(NT, (FILL ? 5 : 8) * 128 / NT) parse_kernel(co
 
   for (u64 s0 = (u64)blockIdx.x * NT; s0 < a.nseq; s0 += (u64)gridDim.x * NT) {
     const u64 s = s0 + (u64)t;
-    bool act = s < a.nseq;
     u64 start = 0;
     int len = 0;
     u32 depth = 1;
-    if (act) {
-      if (a.seg_start) {
-        start = a.seg_start[s];
-        len = (int)a.seg_len[s];
-        if (a.seg_depth) depth = a.seg_depth[s];
-      } else {
-        start = a.offsets[s];
-        len = (int)(a.offsets[s + 1] - start);
-      }
-      if (len < k + 2) act = false;  // kcount.cpp:79 (len < k) and: fewer than k+2 bases hold no counted k-mer
-    }
+    const bool act = seq_header(a, s, start, len, depth);
     int a0 = 0, nk = 0;
-    // ---- 1. load + pack: aligned 16-byte chunks; base q of the sequence sits at stream position a0 + q ----
     if (act) {
-      const uint8_t *src = a.bytes + start;
-      a0 = (int)((uintptr_t)src & 15);
-      const uint4 *p16 = (const uint4 *)(src - a0);
-      const int end = a0 + len;
-      const int n16 = (end + 15) >> 4;
-      for (int c = 0; c < n16; c += 2) {
-        const uint4 v0 = __ldg(p16 + c);
-        const uint4 v1 = (c + 1 < n16) ? __ldg(p16 + c + 1) : make_uint4(0, 0, 0, 0);
-        u32 c0, b0, c1, b1;
-        if (a.ascii) {
-          decode16_ascii(v0, a0 - 16 * c, end - 16 * c, c0, b0, bad);
-          decode16_ascii(v1, a0 - 16 * (c + 1), (c + 1 < n16) ? end - 16 * (c + 1) : 0, c1, b1, bad);
-        } else {
-          decode16_packed(v0, a.qual_add, c0, b0);
-          decode16_packed(v1, a.qual_add, c1, b1);
-        }
-        sb.set(c, c0);
-        sb.set(c + 1, c1);
-        sv.set(c >> 1, b0 | (b1 << 16));
-      }
-      const int nwp = (n16 + 1) & ~1;
-      sb.set(nwp, 0);  // fetch64 may read 2 words past the last base
-      sb.set(nwp + 1, 0);
-      sb.set(nwp + 2, 0);
-      sv.set(nwp >> 1, 0);
-      sv.set((nwp >> 1) + 1, 0);
+      a0 = load_pack<NT>(a, sb, sv, start, len, bad);
       for (int j = 0; j < w; j++) vh[j * NT] = 0;
       nk = len - k - 1;  // k-mers i = 1..nk
       local_inst += (u32)nk;
@@ -195,67 +209,25 @@ __global__ void __launch_bounds__(NT, (FILL ? 5 : 8) * 128 / NT) parse_kernel(co
       f = fetch64(sb, a0) & mmask;  // m-mer at position 0; every step shifts in the base that completes position p
       r = revcomp64(f) << msh;
     }
+    u32 *const el = a.elist + ((u64)(s0 / NT) * (u64)a.ecap) * NT + t;  // this thread's list, entry e at el[e * NT]
+    int ebase = 0;
 
-    // phase B. Supermer e = k-mers [i_e, i_{e+1} - 1]; `fin`: the sequence is done, its last supermer ends at k-mer nk.
+    // Supermer e = k-mers [i_e, i_{e+1} - 1]; `fin`: the sequence is done, its last supermer ends at k-mer nk.
     // Otherwise the last entry stays pending (moved to the front of the list) until the next one arrives.
     auto drain = [&](bool fin) {
       const int ndone = fin ? cnt : max(cnt - 1, 0);
       const int maxd = __reduce_max_sync(FULL, ndone);
-      for (int e0 = 0; e0 < maxd; e0 += 4) {
-        u32 bkt[4], pos_[4], hdr_[4];
-        int i0_[4];
-        u64 base_[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-          const int e = e0 + u;
-          bkt[u] = 0xFFFFFFFFu;
-          if (e < ndone) {
-            const u32 ent = lst[e * NT];
-            const int i0 = (int)(ent >> 8), mp = (int)(ent & 255u);
-            const int i1 = (e + 1 < cnt) ? (int)(lst[(e + 1) * NT] >> 8) - 1 : nk;
-            const int n_k = i1 - i0 + 1;
-            const u32 b = bucket_of(canonical_mmer(fetch64(sb, a0 + mp), m), a.num_shards, a.num_parts);
-            bkt[u] = b;
-            i0_[u] = i0;
-            hdr_[u] = (u32)(n_k + k + 1) | (depth << 16);
-            if (!FILL) {
-              atomicAdd((u64 *)&a.hist[b], 1ULL | ((u64)n_k << 32));
-            } else {
-              pos_[u] = atomicAdd(&a.hist[b].nsup, 1u);
-              base_[u] = __ldg(a.base + b);
-            }
-          }
-        }
-        if (FILL) {
-#pragma unroll
-          for (int u = 0; u < 4; u++) {
-            if (bkt[u] != 0xFFFFFFFFu) {
-              uint4 *dst = (uint4 *)(a.rec + (base_[u] + pos_[u]) * (u64)a.rw);
-              const int q0 = a0 + i0_[u] - 1;  // stream position of the supermer's first base (k-mer i0 - 1's first)
-              const int nb = (int)(hdr_[u] & 0xFFFFu);
-              const int nwb_s = (nb + 15) >> 4, nwv_s = (nb + 31) >> 5;  // words this supermer really fills
-              // word x of the record: 0 = header, 1..nwb = bases, then valid bits; unused words are zero
-              for (int x0 = 0; x0 < a.rw; x0 += 4) {
-                u32 wd[4];
-#pragma unroll
-                for (int y = 0; y < 4; y++) {
-                  const int x = x0 + y;
-                  u32 v = 0;
-                  if (x == 0) v = hdr_[u];
-                  else if (x <= a.nwb) {
-                    if (x - 1 < nwb_s) v = (u32)(fetch64(sb, q0 + 16 * (x - 1)) >> 32);
-                  } else if (x - 1 - a.nwb < nwv_s) {
-                    const int qv = q0 + 32 * (x - 1 - a.nwb);
-                    v = __funnelshift_r(sv[qv >> 5], sv[(qv >> 5) + 1], qv & 31);
-                  }
-                  wd[y] = v;
-                }
-                dst[x0 >> 2] = make_uint4(wd[0], wd[1], wd[2], wd[3]);
-              }
-            }
-          }
+      for (int e = 0; e < maxd; e++) {
+        if (e < ndone) {
+          const u32 ent = lst[e * NT];
+          const int i0 = (int)(ent >> 8), mp = (int)(ent & 255u);
+          const int i1 = (e + 1 < cnt) ? (int)(lst[(e + 1) * NT] >> 8) - 1 : nk;
+          const u32 b = bucket_of(canonical_mmer(fetch64(sb, a0 + mp), m), a.num_shards, a.num_parts);
+          atomicAdd((u64 *)&a.hist[b], 1ULL | ((u64)(i1 - i0 + 1) << 32));
+          el[(size_t)(ebase + e) * NT] = b | ((u32)i0 << 24);
         }
       }
+      ebase += ndone;
       if (!fin && cnt > 0) {
         lst[0] = lst[(cnt - 1) * NT];
         cnt = 1;
@@ -303,11 +275,88 @@ __global__ void __launch_bounds__(NT, (FILL ? 5 : 8) * 128 / NT) parse_kernel(co
       if (__any_sync(FULL, cnt >= PARSE_LCAP)) drain(false);
     }
     drain(true);
+    if (s < a.nseq) a.ecnt[s] = (uint8_t)ebase;
   }
   if (bad) atomicOr(a.err, 1u);
-  if (!FILL) {
-    const u32 tot = __reduce_add_sync(FULL, local_inst);  // < 2^32 per warp for any realistic launch
-    if ((threadIdx.x & 31) == 0 && tot) atomicAdd(a.instances, (u64)tot);
+  const u32 tot = __reduce_add_sync(FULL, local_inst);  // < 2^32 per warp for any realistic launch
+  if ((threadIdx.x & 31) == 0 && tot) atomicAdd(a.instances, (u64)tot);
+}
+
+// Step 3 on its own: the sequence is packed again (it is the cheapest part), its supermers come from the list the parse
+// kernel left. Four supermers per thread are in flight: the bucket-cursor atomics of all four are issued first, then the
+// records are assembled from the 2-bit / valid words in shared memory and written with 128-bit stores.
+// Must run with the grid and block size of the parse kernel that wrote the lists (chunk c = NT consecutive sequences).
+template <int NT>
+__global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs a) {
+  extern __shared__ __align__(16) u32 smem_parse[];
+  const int t = threadIdx.x;
+  const Strided<NT> sb{smem_parse + t};
+  const Strided<NT> sv{smem_parse + a.nsb * NT + t};
+  const unsigned FULL = 0xffffffffu;
+  const int k = a.k;
+  bool bad = false;
+  for (u64 s0 = (u64)blockIdx.x * NT; s0 < a.nseq; s0 += (u64)gridDim.x * NT) {
+    const u64 s = s0 + (u64)t;
+    u64 start = 0;
+    int len = 0;
+    u32 depth = 1;
+    const bool act = seq_header(a, s, start, len, depth);
+    int a0 = 0, nk = 0, cnt = 0;
+    if (act) {
+      a0 = load_pack<NT>(a, sb, sv, start, len, bad);
+      nk = len - k - 1;
+      cnt = (int)a.ecnt[s];
+    }
+    const u32 *const el = a.elist + ((u64)(s0 / NT) * (u64)a.ecap) * NT + t;
+    const int maxd = __reduce_max_sync(FULL, cnt);
+    u32 ent = cnt > 0 ? __ldg(el) : 0u;
+    for (int e0 = 0; e0 < maxd; e0 += 4) {
+      u32 pos_[4], hdr_[4];
+      int i0_[4];
+      bool on[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int e = e0 + u;
+        on[u] = e < cnt;
+        if (on[u]) {
+          const u32 nxt = (e + 1 < cnt) ? __ldg(el + (size_t)(e + 1) * NT) : 0u;
+          const u32 b = ent & 0xFFFFFFu;
+          const int i0 = (int)(ent >> 24);
+          const int i1 = (e + 1 < cnt) ? (int)(nxt >> 24) - 1 : nk;
+          i0_[u] = i0;
+          hdr_[u] = (u32)(i1 - i0 + 1 + k + 1) | (depth << 16);
+          pos_[u] = atomicAdd(&a.cursor[b], 1u);
+          ent = nxt;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        if (on[u]) {
+          uint4 *dst = (uint4 *)(a.rec + (u64)pos_[u] * (u64)a.rw);
+          const int q0 = a0 + i0_[u] - 1;  // stream position of the supermer's first base (k-mer i0 - 1's first)
+          const int nb = (int)(hdr_[u] & 0xFFFFu);
+          const int nwb_s = (nb + 15) >> 4, nwv_s = (nb + 31) >> 5;  // words this supermer really fills
+          // word x of the record: 0 = header, 1..nwb = bases, then valid bits; unused words are zero
+          for (int x0 = 0; x0 < a.rw; x0 += 4) {
+            u32 wd[4];
+#pragma unroll
+            for (int y = 0; y < 4; y++) {
+              const int x = x0 + y;
+              u32 v = 0;
+              if (x == 0) v = hdr_[u];
+              else if (x <= a.nwb) {
+                if (x - 1 < nwb_s) v = (u32)(fetch64(sb, q0 + 16 * (x - 1)) >> 32);
+              } else if (x - 1 - a.nwb < nwv_s) {
+                const int qv = q0 + 32 * (x - 1 - a.nwb);
+                v = __funnelshift_r(sv[qv >> 5], sv[(qv >> 5) + 1], qv & 31);
+              }
+              wd[y] = v;
+            }
+            dst[x0 >> 2] = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+          }
+        }
+      }
+    }
   }
 }
 

@@ -178,6 +178,43 @@ def test_saturation_and_heavy_hitters(built):
     assert gpu[4]["table_retries"] > 0  # the u16 counters wrapped: those work items were re-run with u32 counters
 
 
+def test_skewed_community_c5(built):
+    """BASELINE config C5 in small: Zipf(1.2) abundances, reads from a short repeat and poly-A inserts (heavy-hitter
+    k-mers: a few partitions far above the mean, the 'heavy' schedule and wide counters), 1 % errors."""
+    k = 31
+    com = synth.make_community(200000, n_genomes=50, seed=55, zipf=1.2)
+    rb, ro = synth.make_reads(30000, com, error_rate=0.01, seed=56, n_rate=1e-3)
+    rep = synth.make_community(2000, n_genomes=1, seed=57)
+    rb2, ro2 = synth.make_reads(6000, rep, error_rate=0.01, seed=58)
+    polya = np.full((800, 150), 0 | (31 << 3), dtype=np.uint8)  # poly-A reads: one k-mer, 118 instances per read
+    polya[:, 70] = np.arange(800) % 4 | (31 << 3)               # one variable base: a handful of neighbours
+    rb3 = polya.reshape(-1)
+    rb_all = np.concatenate([rb, rb2, rb3])
+    ro_all = np.concatenate([ro, ro2[1:] + ro[-1], np.arange(1, 801, dtype=np.uint64) * 150 + ro[-1] + ro2[-1]])
+    ref = _oracle(k, rb_all, ro_all, want_prefilter=True)
+    assert ref.pf_vals[:, 0].max() == 65535, "the input is meant to saturate a counter"
+    for parts in (0, 64):
+        gpu = _gpu(k, rb_all, ro_all, num_partitions=parts, keep_prefilter=True)
+        _assert_same(gpu, ref, f"C5 parts={parts}")
+        assert np.array_equal(gpu[5][0], ref.pf_keys) and np.array_equal(gpu[5][1], ref.pf_vals)
+        assert gpu[4]["dropped"] == 0
+
+
+@pytest.mark.parametrize("name", ["kcount_k21_reads", "kcount_k31_ctgs", "kcount_k33_reads", "kcount_k55_ctgs", "kcount_k99_ctgs"])
+def test_against_committed_golden_tables(built, name):
+    """The CUDA path against tests/golden/ (tables written by the reference's own kcount_cpu.cpp build, make_golden.py):
+    no oracle in the loop."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz"))
+    kw = {}
+    if "ctg_seqs" in g:
+        kw = dict(ctg_seqs=g["ctg_seqs"], ctg_offsets=g["ctg_offsets"], ctg_depths=g["ctg_depths"])
+    keys, counts, left, right, st, pf = _gpu(int(g["k"]), g["read_bytes"], g["read_offsets"], keep_prefilter=True, **kw)
+    assert np.array_equal(keys, g["keys"]) and np.array_equal(counts, g["counts"])
+    assert np.array_equal(left, g["left"]) and np.array_equal(right, g["right"])
+    assert np.array_equal(pf[0], g["pf_keys"]) and np.array_equal(pf[1], g["pf_vals"])
+
+
 def test_edge_cases(built, community):
     from mhm2_proxy_b200 import kcount
     k = 31
