@@ -543,6 +543,10 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   if (hs >> 32) return fail(h, KC_ERR_INVALID, "internal: %llu supermers in one batch do not fit the 32-bit bucket cursors", (unsigned long long)hs);
   // FILL
   a.cursor = (u32 *)h->d_cursor.p;
+  {
+    static const int hint = getenv("KC_FILL_L2_HINT") ? atoi(getenv("KC_FILL_L2_HINT")) : 1;  // A/B switch (tools/prof_run.py)
+    a.l2_hint = hint;
+  }
   a.rec = blk.rec;
   CK(cudaEventRecord(h->ev_d, h->s_main));
   k_fill<<<grid_fill, threads, smem_fill, h->s_main>>>(a);

@@ -64,6 +64,7 @@ struct ParseArgs {
   int nwb, nwv, rw;        // record geometry
   BucketHist *hist;        // parse: bucket histogram (+=)
   u32 *cursor;             // fill: index of the next free record of every bucket (starts at the bucket's first record)
+  int l2_hint;             // fill: record stores carry an L2 evict_last policy
   u32 *rec;                // fill: records
   u32 *elist;              // supermer lists: entry e of the sequence handled by thread t of chunk c (= NT consecutive
   int ecap;                //   sequences) at elist[((u64)c * ecap + e) * NT + t]; ecap = longest sequence - k - 1
@@ -124,6 +125,32 @@ __device__ __forceinline__ void decode16_ascii(const uint4 v, int lo, int hi, u3
     vbits |= (u32)(acgt && !(b & 0x20u)) << i;
     if (i >= lo && i < hi && !acgt && up != 'N') bad = true;
   }
+}
+
+// L2 residency hints of the fill kernel. A record store fills half (k <= 31) or all of a 32-byte sector of a bucket that
+// receives its next record microseconds later: sectors evicted half-written cost a DRAM read-modify-write (ncu, v12: 5.2 GB
+// read + 6.9 GB written for 2.3 + 4.6 GB of algorithmic traffic at k=21). Record stores therefore ask L2 to evict them last,
+// the streaming list reads to evict them first.
+__device__ __forceinline__ u64 l2_policy_evict_last() {
+  u64 pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void st_record(uint4 *p, const uint4 v, int hint, u64 pol) {
+  if (hint)
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol) : "memory");
+  else
+    *p = v;
+}
+__device__ __forceinline__ u64 l2_policy_evict_first() {
+  u64 pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ u32 ldg_stream(const u32 *p, u64 pol) {
+  u32 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+  return v;
 }
 
 // sequence s of the launch: where it starts, how long it is, its depth; false when it holds no counted k-mer
@@ -295,6 +322,7 @@ __global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs 
   const unsigned FULL = 0xffffffffu;
   const int k = a.k;
   bool bad = false;
+  const u64 pol = l2_policy_evict_last(), pol_first = l2_policy_evict_first();
   for (u64 s0 = (u64)blockIdx.x * NT; s0 < a.nseq; s0 += (u64)gridDim.x * NT) {
     const u64 s = s0 + (u64)t;
     u64 start = 0;
@@ -309,32 +337,21 @@ __global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs 
     }
     const u32 *const el = a.elist + ((u64)(s0 / NT) * (u64)a.ecap) * NT + t;
     const int maxd = __reduce_max_sync(FULL, cnt);
-    u32 ent = cnt > 0 ? __ldg(el) : 0u;
-    for (int e0 = 0; e0 < maxd; e0 += 4) {
-      u32 pos_[4], hdr_[4];
-      int i0_[4];
-      bool on[4];
+    // list entries e0 .. e0+4 of the current group (the fifth closes the fourth supermer); the next group's are requested
+    // before this group's atomics are issued, so that a group costs one memory round trip, not one per supermer
+    u32 cur[5];
+#pragma unroll
+    for (int u = 0; u < 5; u++) cur[u] = (u < cnt) ? ldg_stream(el + (size_t)u * NT, pol_first) : 0u;
+    // records of the previous group: written only after this group's atomics are in flight (their own atomics have had a
+    // whole iteration to return). meta = first k-mer | bases << 8, 0 = no record.
+    u32 ppos[4], pmeta[4] = {0u, 0u, 0u, 0u};
+    auto write_records = [&]() {
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        const int e = e0 + u;
-        on[u] = e < cnt;
-        if (on[u]) {
-          const u32 nxt = (e + 1 < cnt) ? __ldg(el + (size_t)(e + 1) * NT) : 0u;
-          const u32 b = ent & 0xFFFFFFu;
-          const int i0 = (int)(ent >> 24);
-          const int i1 = (e + 1 < cnt) ? (int)(nxt >> 24) - 1 : nk;
-          i0_[u] = i0;
-          hdr_[u] = (u32)(i1 - i0 + 1 + k + 1) | (depth << 16);
-          pos_[u] = atomicAdd(&a.cursor[b], 1u);
-          ent = nxt;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        if (on[u]) {
-          uint4 *dst = (uint4 *)(a.rec + (u64)pos_[u] * (u64)a.rw);
-          const int q0 = a0 + i0_[u] - 1;  // stream position of the supermer's first base (k-mer i0 - 1's first)
-          const int nb = (int)(hdr_[u] & 0xFFFFu);
+        if (pmeta[u]) {
+          uint4 *dst = (uint4 *)(a.rec + (u64)ppos[u] * (u64)a.rw);
+          const int q0 = a0 + (int)(pmeta[u] & 255u) - 1;  // stream position of the supermer's first base (k-mer i0 - 1's first)
+          const int nb = (int)(pmeta[u] >> 8);
           const int nwb_s = (nb + 15) >> 4, nwv_s = (nb + 31) >> 5;  // words this supermer really fills
           // word x of the record: 0 = header, 1..nwb = bases, then valid bits; unused words are zero
           for (int x0 = 0; x0 < a.rw; x0 += 4) {
@@ -343,7 +360,7 @@ __global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs 
             for (int y = 0; y < 4; y++) {
               const int x = x0 + y;
               u32 v = 0;
-              if (x == 0) v = hdr_[u];
+              if (x == 0) v = (u32)nb | (depth << 16);
               else if (x <= a.nwb) {
                 if (x - 1 < nwb_s) v = (u32)(fetch64(sb, q0 + 16 * (x - 1)) >> 32);
               } else if (x - 1 - a.nwb < nwv_s) {
@@ -352,11 +369,37 @@ __global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs 
               }
               wd[y] = v;
             }
-            dst[x0 >> 2] = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+            st_record(dst + (x0 >> 2), make_uint4(wd[0], wd[1], wd[2], wd[3]), a.l2_hint, pol);
           }
         }
       }
+    };
+    for (int e0 = 0; e0 < maxd; e0 += 4) {
+      u32 nxt[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) nxt[u] = (e0 + 5 + u < cnt) ? ldg_stream(el + (size_t)(e0 + 5 + u) * NT, pol_first) : 0u;
+      u32 npos[4], nmeta[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int e = e0 + u;
+        nmeta[u] = 0u;
+        npos[u] = 0u;
+        if (e < cnt) {
+          const u32 b = cur[u] & 0xFFFFFFu;
+          const int i0 = (int)(cur[u] >> 24);
+          const int i1 = (e + 1 < cnt) ? (int)(cur[u + 1] >> 24) - 1 : nk;
+          nmeta[u] = (u32)i0 | ((u32)(i1 - i0 + 1 + k + 1) << 8);
+          npos[u] = atomicAdd(&a.cursor[b], 1u);
+        }
+      }
+      cur[0] = cur[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) cur[u + 1] = nxt[u];
+      write_records();
+#pragma unroll
+      for (int u = 0; u < 4; u++) { ppos[u] = npos[u]; pmeta[u] = nmeta[u]; }
     }
+    write_records();
   }
 }
 
