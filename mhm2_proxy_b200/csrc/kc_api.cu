@@ -322,7 +322,7 @@ namespace {
 // shared-memory table geometry of the count stage for this handle (kc_count.cuh): how many distinct k-mers one work item holds
 void table_geometry(const kc_handle *h, bool wide, bool ctg, u32 &tab_size, u32 &key_cap) {
   const int KW = h->KW, VW = (wide ? VR_WIDE : VR_NARROW) + (ctg ? V_CTG : 0);
-  const size_t budget = (size_t)h->smem_optin - 2048;  // static shared memory + alignment slack
+  const size_t budget = (size_t)h->smem_optin - COUNT_STATIC_SMEM;  // the kernel's static arrays + alignment slack
   const size_t fixed = count_smem_bytes(KW, VW, 0, 0) + 32;
   const size_t per_key = (size_t)KW * 8 + (size_t)VW * 4 + 8;  // + two 4-byte index-table entries (load <= 0.5)
   u64 cap = budget > fixed ? (budget - fixed) / per_key : 16;
@@ -546,6 +546,8 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   {
     static const int hint = getenv("KC_FILL_L2_HINT") ? atoi(getenv("KC_FILL_L2_HINT")) : 1;  // A/B switch (tools/prof_run.py)
     a.l2_hint = hint;
+    static const int pair = getenv("KC_FILL_PAIR") ? atoi(getenv("KC_FILL_PAIR")) : 1;
+    a.pair_lanes = pair;
   }
   a.rec = blk.rec;
   CK(cudaEventRecord(h->ev_d, h->s_main));

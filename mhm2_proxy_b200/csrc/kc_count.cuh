@@ -98,11 +98,13 @@ struct CountArgs {
   u64 pf_cap;
 };
 
+// dynamic shared memory of the count kernel: index table + dense key store + counters. The staging buffers, the instance
+// lists and the segment cache are static arrays (COUNT_STATIC_SMEM): their addresses are compile-time constants + a
+// per-thread offset, which the 64-register budget of a 1024-thread CTA would otherwise re-derive inside the hot loops.
 __host__ __device__ inline size_t count_smem_bytes(int KW, int VW, u32 tab_size, u32 key_cap) {
-  size_t b = (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4) + 8;
-  b += (size_t)SEG_CACHE * sizeof(SegDesc) + (size_t)CNT_GROUPS * ((GRP_STAGE_WORDS + 4) * 4 + GRP_EXP * 2);
-  return b;
+  return (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4) + 8;
 }
+constexpr size_t COUNT_STATIC_SMEM = 27 * 1024;  // >= the kernel's static arrays (checked by the launch: cudaFuncGetAttributes)
 
 __device__ __forceinline__ void group_barrier(int g) {
   asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(GRP_THREADS) : "memory");
@@ -133,11 +135,11 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u32 *tab = (u32 *)smem_raw;                              // [tab_size], 16-byte buckets
-  u32 *stage_all = tab + a.tab_size;                       // [GROUPS][GRP_STAGE_WORDS + 4], 16-byte aligned
-  uint16_t *expl_all = (uint16_t *)(stage_all + CNT_GROUPS * (GRP_STAGE_WORDS + 4));  // [GROUPS][GRP_EXP]
-  u64 *keys = (u64 *)(expl_all + CNT_GROUPS * GRP_EXP);    // [key_cap * KW]
+  u64 *keys = (u64 *)(tab + a.tab_size);                   // [key_cap * KW]
   u32 *vals = (u32 *)(keys + (size_t)a.key_cap * KW);      // [key_cap * VW]
-  SegDesc *segc = (SegDesc *)(vals + (size_t)a.key_cap * VW + ((a.key_cap * VW) & 1));  // [SEG_CACHE], 8-byte aligned
+  __shared__ __align__(16) u32 stage_all[CNT_GROUPS][GRP_STAGE_WORDS + 4];
+  __shared__ uint16_t expl_all[CNT_GROUPS][GRP_EXP];
+  __shared__ __align__(8) SegDesc segc[SEG_CACHE];
   __shared__ u64 s_obase[2];
   __shared__ u32 s_ocur[2];
   __shared__ __align__(16) WorkItem s_work;
@@ -146,8 +148,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int grp = tid / GRP_THREADS, gt = tid % GRP_THREADS, gw = gt >> 5;
-  u32 *stage = stage_all + grp * (GRP_STAGE_WORDS + 4);
-  uint16_t *expl = expl_all + grp * GRP_EXP;
+  u32 *stage = stage_all[grp];
+  uint16_t *expl = expl_all[grp];
   const int k = a.k, rw = a.rw;
   const int nw = KW == 1 ? 1 : (k + 31) >> 5;  // words of the key that hold bases: KW, or KW - 1 when k % 32 == 0
   const u64 last_mask = (k & 31) ? (~0ULL << (64 - 2 * (k & 31))) : ~0ULL;

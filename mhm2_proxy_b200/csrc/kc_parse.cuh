@@ -65,6 +65,7 @@ struct ParseArgs {
   BucketHist *hist;        // parse: bucket histogram (+=)
   u32 *cursor;             // fill: index of the next free record of every bucket (starts at the bucket's first record)
   int l2_hint;             // fill: record stores carry an L2 evict_last policy
+  int pair_lanes;          // fill: 32-byte records are written as whole sectors by lane pairs
   u32 *rec;                // fill: records
   u32 *elist;              // supermer lists: entry e of the sequence handled by thread t of chunk c (= NT consecutive
   int ecap;                //   sequences) at elist[((u64)c * ecap + e) * NT + t]; ecap = longest sequence - k - 1
@@ -345,32 +346,58 @@ __global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs 
     // records of the previous group: written only after this group's atomics are in flight (their own atomics have had a
     // whole iteration to return). meta = first k-mer | bases << 8, 0 = no record.
     u32 ppos[4], pmeta[4] = {0u, 0u, 0u, 0u};
+    // word x of the record of a supermer that starts at stream position q0 and has nb bases: 0 = header, 1..nwb = bases,
+    // then valid bits; unused words are zero
+    auto rec_word = [&](int x, int q0, int nb) -> u32 {
+      const int nwb_s = (nb + 15) >> 4, nwv_s = (nb + 31) >> 5;  // words this supermer really fills
+      if (x == 0) return (u32)nb | (depth << 16);
+      if (x <= a.nwb) return (x - 1 < nwb_s) ? (u32)(fetch64(sb, q0 + 16 * (x - 1)) >> 32) : 0u;
+      if (x - 1 - a.nwb < nwv_s) {
+        const int qv = q0 + 32 * (x - 1 - a.nwb);
+        return __funnelshift_r(sv[qv >> 5], sv[(qv >> 5) + 1], qv & 31);
+      }
+      return 0u;
+    };
     auto write_records = [&]() {
+      if (a.rw == 8 && a.pair_lanes) {
+        // 32-byte records (k = 32..47): a record is one DRAM sector. Written by its own thread it arrives at L2 as two
+        // half-sector stores; here neighbouring lanes swap halves so that every store instruction carries whole sectors:
+        // first the even lane's record (even lane: words 0-3, odd lane: words 4-7), then the odd lane's.
+        const bool odd = (t & 1) != 0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const bool have = pmeta[u] != 0u;
+          const int q0 = a0 + (int)(pmeta[u] & 255u) - 1;
+          const int nb = (int)(pmeta[u] >> 8);
+          u32 wd[8];
+#pragma unroll
+          for (int x = 0; x < 8; x++) wd[x] = have ? rec_word(x, q0, nb) : 0u;
+          const u64 mydst = (u64)(a.rec + (u64)ppos[u] * 8u);
+          const u64 odst = __shfl_xor_sync(FULL, mydst, 1);
+          const bool ohave = __shfl_xor_sync(FULL, (int)have, 1) != 0;
+          u32 rcv[4];
+#pragma unroll
+          for (int i = 0; i < 4; i++) rcv[i] = __shfl_xor_sync(FULL, odd ? wd[i] : wd[4 + i], 1);
+          // record of the even lane
+          if (odd ? ohave : have)
+            st_record((uint4 *)(odd ? odst + 16 : mydst), odd ? make_uint4(rcv[0], rcv[1], rcv[2], rcv[3]) : make_uint4(wd[0], wd[1], wd[2], wd[3]),
+                      a.l2_hint, pol);
+          // record of the odd lane
+          if (odd ? have : ohave)
+            st_record((uint4 *)(odd ? mydst + 16 : odst), odd ? make_uint4(wd[4], wd[5], wd[6], wd[7]) : make_uint4(rcv[0], rcv[1], rcv[2], rcv[3]),
+                      a.l2_hint, pol);
+        }
+        return;
+      }
 #pragma unroll
       for (int u = 0; u < 4; u++) {
         if (pmeta[u]) {
           uint4 *dst = (uint4 *)(a.rec + (u64)ppos[u] * (u64)a.rw);
           const int q0 = a0 + (int)(pmeta[u] & 255u) - 1;  // stream position of the supermer's first base (k-mer i0 - 1's first)
           const int nb = (int)(pmeta[u] >> 8);
-          const int nwb_s = (nb + 15) >> 4, nwv_s = (nb + 31) >> 5;  // words this supermer really fills
-          // word x of the record: 0 = header, 1..nwb = bases, then valid bits; unused words are zero
-          for (int x0 = 0; x0 < a.rw; x0 += 4) {
-            u32 wd[4];
-#pragma unroll
-            for (int y = 0; y < 4; y++) {
-              const int x = x0 + y;
-              u32 v = 0;
-              if (x == 0) v = (u32)nb | (depth << 16);
-              else if (x <= a.nwb) {
-                if (x - 1 < nwb_s) v = (u32)(fetch64(sb, q0 + 16 * (x - 1)) >> 32);
-              } else if (x - 1 - a.nwb < nwv_s) {
-                const int qv = q0 + 32 * (x - 1 - a.nwb);
-                v = __funnelshift_r(sv[qv >> 5], sv[(qv >> 5) + 1], qv & 31);
-              }
-              wd[y] = v;
-            }
-            st_record(dst + (x0 >> 2), make_uint4(wd[0], wd[1], wd[2], wd[3]), a.l2_hint, pol);
-          }
+          for (int x0 = 0; x0 < a.rw; x0 += 4)
+            st_record(dst + (x0 >> 2), make_uint4(rec_word(x0, q0, nb), rec_word(x0 + 1, q0, nb), rec_word(x0 + 2, q0, nb), rec_word(x0 + 3, q0, nb)),
+                      a.l2_hint, pol);
         }
       }
     };
