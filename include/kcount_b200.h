@@ -166,7 +166,7 @@ int kc_get_stats(kc_handle *h, kc_stats *st);
 
 /* ---- primitives, exported for known-answer tests of the device code (each runs a tiny kernel) ----
  * kmers: n ASCII k-mers of length k back to back. Outputs per k-mer: words[N_LONGS], rc_words[N_LONGS],
- * minimizer (kmer.cpp:345-393), slot hash = MurmurHash3_x64_64 (kmer.cpp:465-468), owner = quick_hash(minimizer) %
+ * minimizer (kmer.cpp:345-393), hash = Kmer::hash = MurmurHash3_x64_64 (kmer.cpp:465-468; the count stage's own slot hash is internal), owner = quick_hash(minimizer) %
  * num_shards (kmer_dht.cpp:192-196). */
 int kc_prim_kmers(int32_t device, int32_t k, const char *kmers, uint64_t n, int32_t num_shards, uint64_t *words, uint64_t *rc_words,
                   uint64_t *minimizer, uint64_t *hash, int32_t *owner);

@@ -1091,6 +1091,9 @@ int finish_impl(kc_handle *h, HostSink *sink) {
 
 namespace {
 constexpr u32 SINK_SLICES = 8;
+// cumulative slice boundaries in 64ths of the item range: three quarters in big slices, then halving — the copy that
+// nothing overlaps is the LAST slice's, so that one is made small (1/64 of the table)
+constexpr u32 SINK_BOUND64[SINK_SLICES + 1] = {0, 16, 32, 48, 56, 60, 62, 63, 64};
 
 // survivors [sink->copied, upto) are final once `ready` has happened on the main stream: send them to the host on the copy
 // stream while the main stream keeps counting
@@ -1348,7 +1351,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
       CK(cudaEventRecord(h->ev_c, h->s_main));
       for (u32 g = 0; g < G; g++) {
         CountArgs cg = ca;
-        const size_t lo = nitems * g / G, hi = nitems * (g + 1) / G;
+        const size_t lo = G == 1 ? 0 : nitems * SINK_BOUND64[g] / 64, hi = G == 1 ? nitems : nitems * SINK_BOUND64[g + 1] / 64;
         cg.items = ca.items + lo;
         cg.status = ca.status + lo;
         cg.nitems = (u32)(hi - lo);

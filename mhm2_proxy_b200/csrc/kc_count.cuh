@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   __shared__ u32 s_ocur[2];
   __shared__ __align__(16) WorkItem s_work;
   __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed, s_widx;
-  __shared__ u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];
+  __shared__ __align__(16) u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];  // per warp of a pipeline; read as 2 x uint4
   __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int grp = tid / GRP_THREADS, gt = tid % GRP_THREADS, gw = gt >> 5;
@@ -247,10 +247,14 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         }
         if (lane == 31) gw_k[grp][gw] = ik;
         group_barrier(grp);
-        u32 pre = 0;
+        {
+          const uint4 k0 = ((const uint4 *)gw_k[grp])[0], k1 = ((const uint4 *)gw_k[grp])[1];
+          const u32 kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
+          u32 pre = 0;
 #pragma unroll
-        for (int i = 0; i < 8; i++) pre += (i < gw) ? gw_k[grp][i] : 0u;
-        ik += pre;
+          for (int i = 0; i < 7; i++) pre += (i < gw) ? kk[i] : 0u;
+          ik += pre;
+        }
         const bool fits = have && ik <= (u32)GRP_EXP;  // prefix sums are monotone: the fitting ones are a prefix
         const u32 fm = __ballot_sync(0xffffffffu, fits);
         const u32 fsum = __reduce_add_sync(0xffffffffu, fits ? nk : 0u);
@@ -260,9 +264,10 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           for (u32 j = 0; j < nk; j++) expl[koff + j] = (uint16_t)((u32)gt | (j << 8));
         }
         group_barrier(grp);
-        u32 n_take = 0, total = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) { n_take += gw_c[grp][i]; total += gw_s[grp][i]; }
+        const uint4 c0v = ((const uint4 *)gw_c[grp])[0], c1v = ((const uint4 *)gw_c[grp])[1];
+        const uint4 s0v = ((const uint4 *)gw_s[grp])[0], s1v = ((const uint4 *)gw_s[grp])[1];
+        const u32 n_take = (c0v.x + c0v.y) + (c0v.z + c0v.w) + (c1v.x + c1v.y) + (c1v.z + c1v.w);
+        const u32 total = (s0v.x + s0v.y) + (s0v.z + s0v.w) + (s1v.x + s1v.y) + (s1v.z + s1v.w);
 
         // ---- c. every k-mer instance of the chunk ----
         for (u32 t = gt; t < total; t += GRP_THREADS) {
@@ -354,8 +359,10 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
               }
             }
             if (idx != 0xFFFFFFFFu) break;
-            const u32 em = (bq.x == 0 ? 1u : 0u) | (bq.y == 0 ? 2u : 0u) | (bq.z == 0 ? 4u : 0u) | (bq.w == 0 ? 8u : 0u);
-            if (em) {  // the key is not in the table (entries are never removed): claim the bucket's first empty entry
+            // entries of a bucket are claimed in order and never removed, so the occupied ones are a prefix: the bucket has
+            // room iff its last entry is empty, and the first empty entry is the number of occupied ones (a stale view can
+            // only point at an entry that is already taken: the CAS fails and the bucket is read again)
+            if (bq.w == 0u) {  // the key is not in the table: claim the bucket's first empty entry
               if (mine == 0xFFFFFFFFu) {  // reserve a dense entry (or reuse the one a lost race left us), fill it, publish it
                 if (spare != 0xFFFFFFFFu) {
                   mine = spare;
@@ -371,7 +378,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
                 for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
                 __threadfence_block();
               }
-              const u32 q = (u32)__ffs(em) - 1u;
+              const u32 q = (bq.x != 0u ? 1u : 0u) + (bq.y != 0u ? 1u : 0u) + (bq.z != 0u ? 1u : 0u);
               if (atomicCAS(&tab[4 * bkt + q], 0u, fp | (mine + 1u)) == 0u) {
                 idx = mine;
                 claimed = true;
@@ -448,7 +455,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       const bool occ = idx < n && kp[KW - 1] != KEY_EMPTY;
       bool survive = false;
       u32 count = 0, rcount = 0;
-      char le = 'X', re = 'X';
+      u32 lc = 5u, rc_ = 5u;  // extension codes: A C G T F X
       u32 L[4] = {0, 0, 0, 0}, R[4] = {0, 0, 0, 0};
       if (occ) {
         const u32 *v = vals + (size_t)idx * VW;
@@ -470,8 +477,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           if (cn) {
             bool use_ctg = (tot == 0) || (count == 1);  // new, or singleton read k-mer (kcount_cpu.cpp:365-371)
             if (!use_ctg) {
-              const char l0 = get_ext(L, count, a.dmin_thres, a.frac), r0 = get_ext(R, count, a.dmin_thres, a.frac);
-              use_ctg = (l0 == 'X' || l0 == 'F' || r0 == 'X' || r0 == 'F');  // non-UU read k-mer (kcount_cpu.cpp:373-376)
+              const int dm0 = dmin_dyn_of(count, a.dmin_thres, a.frac);
+              use_ctg = ext_code(L, dm0) >= 4u || ext_code(R, dm0) >= 4u;  // non-UU read k-mer: an X or F side (kcount_cpu.cpp:373-376)
             }
             if (use_ctg) {
               // closed form of the sequential rules kcount_cpu.cpp:378-404 (DESIGN.md "contig pass")
@@ -492,16 +499,15 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           }
         }
         if (count >= 2) {
-          le = get_ext(L, count, a.dmin_thres, a.frac);
-          re = get_ext(R, count, a.dmin_thres, a.frac);
-          survive = !(le == 'X' && re == 'X');
+          const int dm = dmin_dyn_of(count, a.dmin_thres, a.frac);
+          lc = ext_code(L, dm);
+          rc_ = ext_code(R, dm);
+          survive = !(lc == 5u && rc_ == 5u);
         }
       }
       const bool pf = a.pf_keys && occ && rcount > 0;  // k-mers seen in reads (the table as it stands after the reads pass)
       // verdict of this key, parked in the index table (no longer needed: insertion is over) until output space is reserved
       if (idx < n) {
-        const u32 lc = le == 'A' ? 0u : le == 'C' ? 1u : le == 'G' ? 2u : le == 'T' ? 3u : le == 'F' ? 4u : 5u;
-        const u32 rc_ = re == 'A' ? 0u : re == 'C' ? 1u : re == 'G' ? 2u : re == 'T' ? 3u : re == 'F' ? 4u : 5u;
         tab[idx] = (count & 0xFFFFu) | (lc << 16) | (rc_ << 19) | (survive ? 1u << 22 : 0u) | (pf ? 1u << 23 : 0u);
       }
       n_occ += occ ? 1u : 0u;

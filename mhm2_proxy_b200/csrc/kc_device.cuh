@@ -168,26 +168,34 @@ __device__ __forceinline__ u64 canonical_mmer(u64 x, int m) {
 // ExtCounts::get_ext (kcount_cpu.cpp:135-145,173-182): order the four counters descending, ties to the LARGER letter
 // (T > G > C > A); dmin_dyn = max((int)((1.0 - DYN_MIN_DEPTH) * count), dmin_thres) in IEEE fp64 — `frac` is the host's
 // (1.0 - dyn_min_depth), so 0.09999999999999998 for 0.9, and there is one multiply (no contraction possible).
-__host__ __device__ __forceinline__ char get_ext(const u32 *e, u32 count, int dmin_thres, double frac) {
-  // (value, index) kept in registers: indexing e[] with a run-time `top` would put the caller's counters in local memory
-  int top = 3;  // start from T so that ties keep the larger letter
-  u32 best = e[3];
-#pragma unroll
-  for (int i = 2; i >= 0; i--)
-    if (e[i] > best) { best = e[i]; top = i; }
-  u32 runner = 0;
-#pragma unroll
-  for (int i = 0; i < 4; i++)
-    if (i != top && e[i] > runner) runner = e[i];
+// dmin_dyn of a k-mer: one IEEE fp64 multiply, truncation, floor at dmin_thres — shared by its left and right side
+__host__ __device__ __forceinline__ int dmin_dyn_of(u32 count, int dmin_thres, double frac) {
 #ifdef __CUDA_ARCH__
   int dmin_dyn = (int)__dmul_rn(frac, (double)count);
 #else
   int dmin_dyn = (int)(frac * (double)count);
 #endif
-  if (dmin_dyn < dmin_thres) dmin_dyn = dmin_thres;
-  if ((int)best < dmin_dyn) return 'X';
-  if ((int)runner >= dmin_dyn) return 'F';
-  return top == 0 ? 'A' : top == 1 ? 'C' : top == 2 ? 'G' : 'T';
+  return dmin_dyn < dmin_thres ? dmin_thres : dmin_dyn;
+}
+// extension code of one side: 0..3 = A C G T, 4 = 'F' (fork), 5 = 'X' (none)
+__host__ __device__ __forceinline__ u32 ext_code(const u32 *e, int dmin_dyn) {
+  // (value, index) kept in registers: indexing e[] with a run-time `top` would put the caller's counters in local memory
+  u32 top = 3;  // start from T so that ties keep the larger letter
+  u32 best = e[3];
+#pragma unroll
+  for (int i = 2; i >= 0; i--)
+    if (e[i] > best) { best = e[i]; top = (u32)i; }
+  u32 runner = 0;
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+    if ((u32)i != top && e[i] > runner) runner = e[i];
+  if ((int)best < dmin_dyn) return 5u;
+  if ((int)runner >= dmin_dyn) return 4u;
+  return top;
+}
+__host__ __device__ __forceinline__ char ext_char_of(u32 c) { return c < 4u ? (char)((0x54474341u >> (8u * c)) & 0xFFu) : (c == 4u ? 'F' : 'X'); }
+__host__ __device__ __forceinline__ char get_ext(const u32 *e, u32 count, int dmin_thres, double frac) {
+  return ext_char_of(ext_code(e, dmin_dyn_of(count, dmin_thres, frac)));
 }
 
 __device__ __forceinline__ u32 sat16(u64 v) { return v > 65535ULL ? 65535u : (u32)v; }

@@ -15,7 +15,7 @@
 //   3. phase B, per group of 4 list entries and converged across lanes: recompute the m-mer, bucket =
 //      (quick_hash(minimizer) % num_shards, partition from the high half of the same hash), reserve a record slot in
 //      the bucket (ONE 32-bit atomic), build the fixed-size record in registers and write it with 16-byte stores.
-// Supermer record = rw u32 words (rw % 4 == 0, 16-byte aligned; k=21: exactly 16 bytes):
+// Supermer record = rw u32 words (k <= 21: 4 words = 16 bytes; else a multiple of 8 words = whole 32-byte sectors):
 //      word 0: nb (bases, = k-mers + k + 1) | depth << 16     (depth: 1 for reads, contig depth for contig supermers)
 //      words 1 .. nwb: 2-bit bases, 16 per word, MSB first     (nwb = ceil(nb_max / 16), nb_max = w + k + 1)
 //      words 1+nwb .. : "extension-valid" bits, LSB first      (nwv = ceil(nb_max / 32))
@@ -42,7 +42,8 @@ __host__ __device__ inline RecGeom rec_geom(int k, int w) {
   g.nb_max = w + k + 1;
   g.nwb = (g.nb_max + 15) >> 4;
   g.nwv = (g.nb_max + 31) >> 5;
-  g.rw = (1 + g.nwb + g.nwv + 3) & ~3;
+  const int need = 1 + g.nwb + g.nwv;
+  g.rw = need <= 4 ? 4 : (need + 7) & ~7;  // 16 bytes (k <= 21), else whole 32-byte sectors: see fill_kernel's lane-pair stores
   return g;
 }
 
@@ -65,7 +66,7 @@ struct ParseArgs {
   BucketHist *hist;        // parse: bucket histogram (+=)
   u32 *cursor;             // fill: index of the next free record of every bucket (starts at the bucket's first record)
   int l2_hint;             // fill: record stores carry an L2 evict_last policy
-  int pair_lanes;          // fill: 32-byte records are written as whole sectors by lane pairs
+  int pair_lanes;          // fill: records of whole 32-byte sectors are written sector by sector by lane pairs
   u32 *rec;                // fill: records
   u32 *elist;              // supermer lists: entry e of the sequence handled by thread t of chunk c (= NT consecutive
   int ecap;                //   sequences) at elist[((u64)c * ecap + e) * NT + t]; ecap = longest sequence - k - 1
@@ -359,33 +360,36 @@ __global__ void __launch_bounds__(NT, 8 * 128 / NT) fill_kernel(const ParseArgs 
       return 0u;
     };
     auto write_records = [&]() {
-      if (a.rw == 8 && a.pair_lanes) {
-        // 32-byte records (k = 32..47): a record is one DRAM sector. Written by its own thread it arrives at L2 as two
-        // half-sector stores; here neighbouring lanes swap halves so that every store instruction carries whole sectors:
-        // first the even lane's record (even lane: words 0-3, odd lane: words 4-7), then the odd lane's.
+      if (a.rw >= 8 && a.pair_lanes) {
+        // Records of whole 32-byte sectors (k >= 22). Written by its own thread a sector arrives at L2 as two half-sector
+        // stores, and L2 takes ~41 G store requests/s whatever their size (tools/ubench_scatter.cu: 32-byte records, one
+        // thread 35 G records/s, lane pairs 67 G/s). Neighbouring lanes therefore swap halves, so that every store
+        // instruction carries whole sectors: first the even lane's sector (even lane: words 0-3, odd lane: words 4-7),
+        // then the odd lane's.
         const bool odd = (t & 1) != 0;
 #pragma unroll
         for (int u = 0; u < 4; u++) {
           const bool have = pmeta[u] != 0u;
           const int q0 = a0 + (int)(pmeta[u] & 255u) - 1;
           const int nb = (int)(pmeta[u] >> 8);
-          u32 wd[8];
-#pragma unroll
-          for (int x = 0; x < 8; x++) wd[x] = have ? rec_word(x, q0, nb) : 0u;
-          const u64 mydst = (u64)(a.rec + (u64)ppos[u] * 8u);
+          const u64 mydst = (u64)(a.rec + (u64)ppos[u] * (u64)a.rw);
           const u64 odst = __shfl_xor_sync(FULL, mydst, 1);
           const bool ohave = __shfl_xor_sync(FULL, (int)have, 1) != 0;
-          u32 rcv[4];
+          for (int x0 = 0; x0 < a.rw; x0 += 8) {
+            u32 wd[8];
 #pragma unroll
-          for (int i = 0; i < 4; i++) rcv[i] = __shfl_xor_sync(FULL, odd ? wd[i] : wd[4 + i], 1);
-          // record of the even lane
-          if (odd ? ohave : have)
-            st_record((uint4 *)(odd ? odst + 16 : mydst), odd ? make_uint4(rcv[0], rcv[1], rcv[2], rcv[3]) : make_uint4(wd[0], wd[1], wd[2], wd[3]),
-                      a.l2_hint, pol);
-          // record of the odd lane
-          if (odd ? have : ohave)
-            st_record((uint4 *)(odd ? mydst + 16 : odst), odd ? make_uint4(wd[4], wd[5], wd[6], wd[7]) : make_uint4(rcv[0], rcv[1], rcv[2], rcv[3]),
-                      a.l2_hint, pol);
+            for (int x = 0; x < 8; x++) wd[x] = have ? rec_word(x0 + x, q0, nb) : 0u;
+            u32 rcv[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) rcv[i] = __shfl_xor_sync(FULL, odd ? wd[i] : wd[4 + i], 1);
+            const u64 off = (u64)x0 * 4u;
+            if (odd ? ohave : have)  // sector of the even lane's record
+              st_record((uint4 *)(odd ? odst + off + 16 : mydst + off),
+                        odd ? make_uint4(rcv[0], rcv[1], rcv[2], rcv[3]) : make_uint4(wd[0], wd[1], wd[2], wd[3]), a.l2_hint, pol);
+            if (odd ? have : ohave)  // sector of the odd lane's record
+              st_record((uint4 *)(odd ? mydst + off + 16 : odst + off),
+                        odd ? make_uint4(wd[4], wd[5], wd[6], wd[7]) : make_uint4(rcv[0], rcv[1], rcv[2], rcv[3]), a.l2_hint, pol);
+          }
         }
         return;
       }
