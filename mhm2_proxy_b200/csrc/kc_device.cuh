@@ -86,9 +86,13 @@ __host__ __device__ __forceinline__ u64 quick_hash(u64 v) {
 // Reverse-complement of 32 bases held MSB-first in a u64 (what TWIN_TABLE does byte-wise, kmer.cpp:66-79,492-497):
 // reverse the order of the 2-bit groups and complement (code -> 3 - code == ~code).
 __device__ __forceinline__ u64 revcomp64(u64 x) {
-  x = __brevll(x);                                                           // reverses bits, also inside each pair
-  x = ((x >> 1) & 0x5555555555555555ULL) | ((x & 0x5555555555555555ULL) << 1);  // restore bit order inside pairs
-  return ~x;
+  // per 32-bit half: BREV reverses all bits (also inside each pair), swapping neighbouring bits restores the pairs, NOT
+  // complements; the halves trade places. No bit crosses a half in the neighbour swap (the masks drop bits 31 / 0), so
+  // this is 2 BREV + 2 x (2 shifts + 1 LOP3) instead of 64-bit shift pairs.
+  const u32 lo = __brev((u32)x), hi = __brev((u32)(x >> 32));
+  const u32 a = ~(((lo >> 1) & 0x55555555u) | ((lo << 1) & 0xAAAAAAAAu));
+  const u32 b = ~(((hi >> 1) & 0x55555555u) | ((hi << 1) & 0xAAAAAAAAu));
+  return ((u64)a << 32) | b;
 }
 __host__ __forceinline__ u64 revcomp64_host(u64 x) {
   u64 r = 0;
