@@ -323,7 +323,7 @@ namespace {
 void table_geometry(const kc_handle *h, bool wide, bool ctg, u32 &tab_size, u32 &key_cap) {
   const int KW = h->KW, VW = (wide ? VR_WIDE : VR_NARROW) + (ctg ? V_CTG : 0);
   const size_t budget = (size_t)h->smem_optin - COUNT_STATIC_SMEM;  // the kernel's static arrays + alignment slack
-  const size_t fixed = count_smem_bytes(KW, VW, 0, 0) + 32;
+  const size_t fixed = count_smem_bytes(KW, VW, h->geom.rw, 0, 0) + 32;
   const size_t per_key = (size_t)KW * 8 + (size_t)VW * 4 + 8;  // + two 4-byte index-table entries (load <= 0.5)
   u64 cap = budget > fixed ? (budget - fixed) / per_key : 16;
   cap = std::min<u64>(cap, IDX_MASK - 1);
@@ -1165,8 +1165,8 @@ int finish_count(kc_handle *h, HostSink *sink) {
     u32 tab_size, key_cap;
     table_geometry(h, false, any_ctg, tab_size, key_cap);
     const int VWp = VR_NARROW + (any_ctg ? V_CTG : 0);
-    const size_t smem_p = count_smem_bytes(KW, VWp, tab_size, key_cap) + 8;
-    struct Probe { double mean = 0; u32 maxk = 0, over = 0; u64 inst = 0; u32 S = 0; };
+    const size_t smem_p = count_smem_bytes(KW, VWp, h->geom.rw, tab_size, key_cap) + 8;
+    struct Probe { double mean = 0, live = 0; u32 maxk = 0, over = 0; u64 inst = 0; u32 S = 0; };
     // count (emitting nothing) a sample of S candidate items of g neighbouring buckets each, spread over the partition space
     auto probe = [&](u32 g, Probe &pr) -> int {
       const u32 nq = (P + g - 1) / g;
@@ -1186,6 +1186,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
       pa.k = h->cfg.kmer_len;
       pa.rw = h->geom.rw;
       pa.nwb = h->geom.nwb;
+      pa.w = h->w;
       pa.tab_size = tab_size;
       pa.key_cap = key_cap;
       pa.dmin_thres = h->cfg.dmin_thres;
@@ -1197,45 +1198,52 @@ int finish_count(kc_handle *h, HostSink *sink) {
       CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
       CK(cudaMemcpyAsync(pst.data(), d_status.p, (size_t)S * sizeof(ItemStatus), cudaMemcpyDeviceToHost, h->s_main));
       CK(cudaStreamSynchronize(h->s_main));
-      u64 sum = 0;
+      u64 sum = 0, live = 0;
       for (auto &x : pst) {
         sum += x.nkeys;
+        if (!x.overflow) live += x.progress;
         pr.maxk = std::max(pr.maxk, x.nkeys);
         pr.over += x.overflow ? 1u : 0u;
       }
       pr.mean = (double)sum / S;
+      pr.live = (double)live / S;
       pr.inst = ctr[CTR_READ_INST] + ctr[CTR_CTG_INST];
       pr.S = S;
       CK(cudaMemsetAsync(d_counters.p, 0, CTR_WORDS * 8, h->s_main));
       CK(cudaMemsetAsync(d_status.p, 0, (size_t)S * sizeof(ItemStatus), h->s_main));
       return KC_OK;
     };
-    // Key slots an item needs = its distinct k-mers + the slots same-key races leave unused; the second term does not grow
-    // with the item, so single buckets overstate what a merged item needs. Probe 1 (single buckets) gives a safe merge
-    // factor; probe 2 tries twice that on real candidates and is accepted only if every sampled item stays clear of the
-    // key store's capacity.
+    // Key slots an item needs = its distinct k-mers + the slots same-key races leave unused. The second term does not grow
+    // with the item (a race needs two copies of a new key in flight at once: in a single bucket, counted in a handful of
+    // warp iterations, that is a third of the keys; in a merged item it is the same few hundred slots), so single buckets
+    // overstate what a merged item needs. Probe 1 (single buckets) reports both terms; the merge factor is sized from
+    // distinct k-mers per bucket + that constant, then probe 2 runs real candidates of that size and the factor is accepted
+    // only if every sampled item stays clear of the key store's capacity (else: one bucket fewer per item, re-probed once,
+    // and finally the conservative factor that scales both terms).
     static const double fill = getenv("KC_TARGET_FILL") ? atof(getenv("KC_TARGET_FILL")) : 0.9;
     Probe p1, p2;
     RC(probe(1, p1));
     u32 g_safe = 1;
     if (!p1.over && p1.inst && p1.mean > 0) g_safe = (u32)std::min(64.0, std::max(1.0, std::floor(fill * key_cap / (1.1 * p1.mean))));
     merge = g_safe;
-    const u32 g_try = std::min<u32>(64, std::min<u32>(P, 2 * g_safe));
-    if (!p1.over && g_try > g_safe) {
+    u32 g_try = g_safe;
+    if (!p1.over && p1.live > 0) {
+      const double dead = std::max(0.0, p1.mean - p1.live);
+      g_try = (u32)std::min(64.0, std::max((double)g_safe, std::floor((fill * key_cap / 1.1 - dead) / p1.live)));
+      g_try = std::min<u32>(g_try, P);
+    }
+    for (int attempt = 0; attempt < 2 && g_try > g_safe; attempt++) {
+      p2 = Probe();
       RC(probe(g_try, p2));
       if (!p2.over && p2.maxk <= 0.95 * key_cap && 1.1 * p2.mean <= fill * key_cap) {
         merge = g_try;
-      } else if (p2.over * 20 <= p2.S && p2.mean > p1.mean) {
-        // slots(g) ~ a + b g through the two measurements: largest g below g_try that keeps the margin (a few sampled
-        // items hitting the capacity only make the fitted slope a little too small)
-        const double bslope = (p2.mean - p1.mean) / (double)(g_try - 1), aoff = p1.mean - bslope;
-        const double g_fit = (fill * key_cap / 1.1 - aoff) / bslope;
-        merge = (u32)std::min<double>(g_try - 1, std::max<double>(g_safe, std::floor(g_fit)));
+        break;
       }
+      g_try--;
     }
     if (getenv("KC_TRACE"))
-      fprintf(stderr, "[kc_trace] probe: P %u key_cap %u | g=1: %.0f slots/item (%u items, %llu inst) -> safe %u | g=%u: mean %.0f max %u over %u"
-              " -> merge %u\n", P, key_cap, p1.mean, p1.S, (unsigned long long)p1.inst, g_safe, g_try, p2.mean, p2.maxk, p2.over, merge);
+      fprintf(stderr, "[kc_trace] probe: P %u key_cap %u | g=1: %.0f slots/item, %.0f distinct (%u items, %llu inst) -> safe %u | g=%u: mean %.0f max %u"
+              " over %u -> merge %u\n", P, key_cap, p1.mean, p1.live, p1.S, (unsigned long long)p1.inst, g_safe, g_try, p2.mean, p2.maxk, p2.over, merge);
     ht.lap("finish: partition probe");
   }
   const u32 NQ = (P + merge - 1) / merge;  // work items
@@ -1285,6 +1293,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
   ca.k = h->cfg.kmer_len;
   ca.rw = h->geom.rw;
   ca.nwb = h->geom.nwb;
+  ca.w = h->w;
   ca.dmin_thres = h->cfg.dmin_thres;
   ca.frac = 1.0 - h->cfg.dyn_min_depth;  // kcount_cpu.cpp:178, evaluated in fp64 exactly as the reference does
   ca.out_keys = (u64 *)h->out_keys.p;
@@ -1317,7 +1326,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
     u32 tab_size, key_cap;
     table_geometry(h, wide, any_ctg, tab_size, key_cap);
     const int VW = (wide ? VR_WIDE : VR_NARROW) + (any_ctg ? V_CTG : 0);
-    const size_t smem = count_smem_bytes(KW, VW, tab_size, key_cap) + 8;
+    const size_t smem = count_smem_bytes(KW, VW, h->geom.rw, tab_size, key_cap) + 8;
     size_t nitems;
     if (first) {
       ca.items = (const WorkItem *)d_items.p;

@@ -32,10 +32,12 @@ namespace kc {
 constexpr u64 KEY_EMPTY = 0xFFFFFFFFFFFFFFFFULL;  // last key word of a real k-mer is never all ones: it has >= 2 zero
                                                   // trailing bits because N_LONGS = k/32 + 1 (main.cpp:170)
 constexpr int CNT_THREADS = 1024;
-constexpr int CNT_GROUPS = 4;          // independent pipelines per CTA
-constexpr int GRP_THREADS = CNT_THREADS / CNT_GROUPS;
-constexpr int GRP_STAGE_WORDS = 1024;  // staged record words per pipeline and chunk
-constexpr int GRP_EXP = 1024;          // k-mer instances per pipeline and chunk
+constexpr int CNT_GROUPS = 32;         // independent pipelines per CTA: every WARP is one (no barrier inside a work item's
+constexpr int GRP_THREADS = CNT_THREADS / CNT_GROUPS;  // stream of supermers: __syncwarp only)
+constexpr int GRP_STAGE_MAX = 256;     // staged record words per pipeline and chunk: min(32 records, this many words) + 4
+constexpr int GRP_EXP = 160;           // k-mer instances per pipeline and chunk
+static_assert(GRP_THREADS == 32, "a pipeline is one warp");
+__host__ __device__ inline int stage_words(int rw) { return (32 * rw < GRP_STAGE_MAX ? 32 * rw : GRP_STAGE_MAX) + 4; }
 constexpr int SEG_CACHE = 64;          // segment descriptors cached per round
 constexpr u32 IDX_BITS = 13, IDX_MASK = (1u << IDX_BITS) - 1u;  // dense index + 1 fits 13 bits: key_cap <= 8190
 constexpr int VR_NARROW = 5, VR_WIDE = 9, V_CTG = 3;
@@ -71,7 +73,7 @@ enum { CTR_SURV = 0, CTR_PF = 1, CTR_DISTINCT = 2, CTR_ERR = 3, CTR_MAXPROBE = 4
 
 struct ItemStatus {
   u32 overflow;  // ran out of key slots: emitted nothing, must be re-run with more sub-passes
-  u32 progress;  // supermers consumed when it overflowed (sizes the retry)
+  u32 progress;  // supermers consumed when it overflowed (sizes the retry); probe run without overflow: distinct k-mers
   u32 nkeys;     // distinct k-mers found (valid when !overflow)
   u32 wide;      // a u16 counter wrapped: emitted nothing, must be re-run with wide counters
 };
@@ -85,6 +87,7 @@ struct CountArgs {
   u32 measure_only;  // probe run: build the tables, report ItemStatus (distinct k-mers), emit nothing
   int k;
   int rw, nwb;     // record geometry (kc_parse.cuh)
+  int w;           // k-mers per supermer <= w (window of the minimizer), mean (w + 1) / 2
   u32 tab_size, key_cap;  // tab_size u32 entries (multiple of 4)
   int dmin_thres;
   double frac;     // 1.0 - DYN_MIN_DEPTH computed on the host in fp64
@@ -98,28 +101,13 @@ struct CountArgs {
   u64 pf_cap;
 };
 
-// dynamic shared memory of the count kernel: index table + dense key store + counters. The staging buffers, the instance
-// lists and the segment cache are static arrays (COUNT_STATIC_SMEM): their addresses are compile-time constants + a
-// per-thread offset, which the 64-register budget of a 1024-thread CTA would otherwise re-derive inside the hot loops.
-__host__ __device__ inline size_t count_smem_bytes(int KW, int VW, u32 tab_size, u32 key_cap) {
-  return (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4) + 8;
+// dynamic shared memory of the count kernel: per-warp staging buffers (first: their addresses are cheap to derive), index
+// table, dense key store, counters. The instance lists and the segment cache are static arrays (COUNT_STATIC_SMEM).
+__host__ __device__ inline size_t count_smem_bytes(int KW, int VW, int rw, u32 tab_size, u32 key_cap) {
+  return (size_t)CNT_GROUPS * stage_words(rw) * 4 + (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4) + 8;
 }
-constexpr size_t COUNT_STATIC_SMEM = 27 * 1024;  // >= the kernel's static arrays (checked by the launch: cudaFuncGetAttributes)
+constexpr size_t COUNT_STATIC_SMEM = 13 * 1024;  // >= the kernel's static arrays (ptxas -v: 12.1 KB)
 
-__device__ __forceinline__ void group_barrier(int g) {
-  asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(GRP_THREADS) : "memory");
-}
-// barrier of one pipeline that also ORs a predicate over its threads: the result is the same in every thread, which a
-// plain read of a flag that another pipeline may be setting concurrently is not
-__device__ __forceinline__ bool group_barrier_or(int g, bool pred) {
-  u32 r;
-  asm volatile(
-      "{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %3, 0;\n\tbar.red.or.pred p, %1, %2, q;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(r)
-      : "r"(g + 1), "r"(GRP_THREADS), "r"((u32)pred)
-      : "memory");
-  return r != 0;
-}
 __device__ __forceinline__ uint4 lds128_volatile(u32 a) {  // a: shared-space address (converted once per kernel)
   uint4 v;
   asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
@@ -134,21 +122,21 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  u32 *tab = (u32 *)smem_raw;                              // [tab_size], 16-byte buckets
+  const int sw = stage_words(a.rw);
+  u32 *stage_all = (u32 *)smem_raw;                        // [CNT_GROUPS][sw], 16-byte aligned rows (sw % 4 == 0)
+  u32 *tab = stage_all + CNT_GROUPS * sw;                  // [tab_size], 16-byte buckets
   u64 *keys = (u64 *)(tab + a.tab_size);                   // [key_cap * KW]
   u32 *vals = (u32 *)(keys + (size_t)a.key_cap * KW);      // [key_cap * VW]
-  __shared__ __align__(16) u32 stage_all[CNT_GROUPS][GRP_STAGE_WORDS + 4];
   __shared__ uint16_t expl_all[CNT_GROUPS][GRP_EXP];
   __shared__ __align__(8) SegDesc segc[SEG_CACHE];
   __shared__ u64 s_obase[2];
   __shared__ u32 s_ocur[2];
   __shared__ __align__(16) WorkItem s_work;
   __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed, s_widx;
-  __shared__ __align__(16) u32 gw_k[CNT_GROUPS][8], gw_c[CNT_GROUPS][8], gw_s[CNT_GROUPS][8];  // per warp of a pipeline; read as 2 x uint4
   __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int grp = tid / GRP_THREADS, gt = tid % GRP_THREADS, gw = gt >> 5;
-  u32 *stage = stage_all[grp];
+  const int grp = wid, gt = lane;  // pipeline = warp
+  u32 *stage = stage_all + grp * sw;
   uint16_t *expl = expl_all[grp];
   const int k = a.k, rw = a.rw;
   const int nw = KW == 1 ? 1 : (k + 31) >> 5;  // words of the key that hold bases: KW, or KW - 1 when k % 32 == 0
@@ -157,7 +145,9 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const u32 nbuckets = a.tab_size >> 2;
   const u32 tab_s = (u32)__cvta_generic_to_shared(tab);
   const int nwb = a.nwb;
-  const int sup_per_chunk = min(GRP_THREADS, GRP_STAGE_WORDS / rw);
+  // supermers staged per chunk: what the staging buffer holds, and no more than the instance list will take (a supermer has
+  // (w + 1) / 2 k-mers on average; staging records that do not fit the list means staging them again)
+  const int sup_per_chunk = min(min(GRP_THREADS, GRP_STAGE_MAX / rw), 2 * GRP_EXP / (a.w + 1) + 3);
   u32 my_max_probe = 0;
   // Work items are dealt round-robin to the CTAs: first the heavy list (outlier partitions, heaviest first, so that none of
   // them starts last and becomes the tail), then every item in partition order, skipping the ones the heavy list covered.
@@ -245,29 +235,14 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           const u32 y = __shfl_up_sync(0xffffffffu, ik, d);
           if (lane >= d) ik += y;
         }
-        if (lane == 31) gw_k[grp][gw] = ik;
-        group_barrier(grp);
-        {
-          const uint4 k0 = ((const uint4 *)gw_k[grp])[0], k1 = ((const uint4 *)gw_k[grp])[1];
-          const u32 kk[8] = {k0.x, k0.y, k0.z, k0.w, k1.x, k1.y, k1.z, k1.w};
-          u32 pre = 0;
-#pragma unroll
-          for (int i = 0; i < 7; i++) pre += (i < gw) ? kk[i] : 0u;
-          ik += pre;
-        }
         const bool fits = have && ik <= (u32)GRP_EXP;  // prefix sums are monotone: the fitting ones are a prefix
-        const u32 fm = __ballot_sync(0xffffffffu, fits);
-        const u32 fsum = __reduce_add_sync(0xffffffffu, fits ? nk : 0u);
-        if (lane == 0) { gw_c[grp][gw] = __popc(fm); gw_s[grp][gw] = fsum; }
+        const u32 n_take = (u32)__popc(__ballot_sync(0xffffffffu, fits));
+        const u32 total = __reduce_add_sync(0xffffffffu, fits ? nk : 0u);
         if (fits) {
           const u32 koff = ik - nk;
           for (u32 j = 0; j < nk; j++) expl[koff + j] = (uint16_t)((u32)gt | (j << 8));
         }
-        group_barrier(grp);
-        const uint4 c0v = ((const uint4 *)gw_c[grp])[0], c1v = ((const uint4 *)gw_c[grp])[1];
-        const uint4 s0v = ((const uint4 *)gw_s[grp])[0], s1v = ((const uint4 *)gw_s[grp])[1];
-        const u32 n_take = (c0v.x + c0v.y) + (c0v.z + c0v.w) + (c1v.x + c1v.y) + (c1v.z + c1v.w);
-        const u32 total = (s0v.x + s0v.y) + (s0v.z + s0v.w) + (s1v.x + s1v.y) + (s1v.z + s1v.w);
+        __syncwarp();
 
         // ---- c. every k-mer instance of the chunk ----
         for (u32 t = gt; t < total; t += GRP_THREADS) {
@@ -418,7 +393,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             atomicOr(v + VR + 2, 1u << (l * 5 + r));
           }
         }
-        const bool stop = group_barrier_or(grp, *(volatile u32 *)&s_over != 0);
+        const bool stop = __any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0);  // also orders this chunk's reads of the
+                                                                                   // staging buffer before the next chunk's writes
         c0 += n_take;
         consumed += n_take;
         if (stop) break;
@@ -430,10 +406,17 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
     const bool over = s_over != 0;
     const bool wide_needed = !WIDE && s_wide;
     const u32 n = min(s_nkeys, a.key_cap);
+    if (a.measure_only && !over) {  // probe run: how many of the n slots hold a key (the others were lost to same-key races)
+      u32 live = 0;
+      for (u32 i = tid; i < n; i += CNT_THREADS) live += keys[(size_t)i * KW + KW - 1] != KEY_EMPTY ? 1u : 0u;
+      live = __reduce_add_sync(0xffffffffu, live);
+      if (lane == 0 && live) atomicAdd(&s_live, live);
+      __syncthreads();
+    }
     if (tid == 0) {
       ItemStatus st;
       st.overflow = over ? 1u : 0u;
-      st.progress = s_consumed;
+      st.progress = (a.measure_only && !over) ? s_live : s_consumed;  // probe: distinct k-mers; else: supermers consumed
       st.nkeys = n;
       st.wide = wide_needed ? 1u : 0u;
       a.status[item_idx] = st;
