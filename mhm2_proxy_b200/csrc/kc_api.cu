@@ -1316,7 +1316,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
   bool wide = false, first = true;
   u64 retries_seen = 0;
   int round = 0;
-  DevBuf d_ritems, d_rstatus;
+  DevBuf d_ritems, d_rstatus, d_retry;
   while (first || !items.empty() || !wide_items.empty()) {
     if (!first && items.empty()) {  // narrow rounds are done: re-run the items whose u16 counters wrapped with u32 counters
       items.swap(wide_items);
@@ -1348,6 +1348,9 @@ int finish_count(kc_handle *h, HostSink *sink) {
     ca.nitems = (u32)nitems;
     ca.tab_size = tab_size;
     ca.key_cap = key_cap;
+    RC(ensure(h, d_retry, std::max<size_t>(nitems, 1) * sizeof(RetryRec)));
+    ca.retry = (RetryRec *)d_retry.p;
+    ca.retry_base = retries_seen;
     if (nitems) {
       // With a host sink the device-built round runs as a few slices of the partition range: the survivors of slice g travel
       // to the host while slice g+1 is being counted (the heavy list belongs to slice 0).
@@ -1390,20 +1393,18 @@ int finish_count(kc_handle *h, HostSink *sink) {
     h->st.table_bytes_max = std::max<u64>(h->st.table_bytes_max, smem);
     std::vector<WorkItem> again;
     if (ctr[CTR_RETRY] != retries_seen) {
+      // the kernel listed the items that have to run again (descriptor + status): the host reads those few records only
+      const size_t n_new = (size_t)(ctr[CTR_RETRY] - retries_seen);
       retries_seen = ctr[CTR_RETRY];
-      if (first) {
-        items.resize(nitems);
-        CK(cudaMemcpy(items.data(), d_items.p, nitems * sizeof(WorkItem), cudaMemcpyDeviceToHost));
-      }
-      status.resize(nitems);
-      CK(cudaMemcpy(status.data(), ca.status, nitems * sizeof(ItemStatus), cudaMemcpyDeviceToHost));
-      for (size_t i = 0; i < nitems; i++) {
-        WorkItem it = items[i];
+      std::vector<RetryRec> recs(n_new);
+      CK(cudaMemcpy(recs.data(), d_retry.p, n_new * sizeof(RetryRec), cudaMemcpyDeviceToHost));
+      for (const RetryRec &r : recs) {
+        WorkItem it = r.item;
         it.heavy = 0;
-        if (status[i].overflow) {
+        if (r.st.overflow) {
           // it filled its key store after `progress` of `nsup` supermers: split its hash range so that each child should
           // end up around 60 % full
-          const double frac_done = std::max(1.0, (double)status[i].progress) / (double)it.nsup;
+          const double frac_done = std::max(1.0, (double)r.st.progress) / (double)it.nsup;
           u32 f = 2;
           while (f < 256 && (double)f * frac_done < 1.6) f <<= 1;
           if ((u64)it.nsub * f > (1u << 20)) return fail(h, KC_ERR_CUDA, "partition %u cannot be split further", it.part);
@@ -1414,7 +1415,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
             again.push_back(ch);
           }
           h->st.table_retries++;
-        } else if (status[i].wide) {
+        } else if (r.st.wide) {
           wide_items.push_back(it);
           h->st.table_retries++;
         }
@@ -1430,7 +1431,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
     CK(cudaStreamSynchronize(h->s_copy));
   }
   h->st.ms_finish += elapsed(e0, e1);
-  for (DevBuf *b : {&d_counters, &d_segs, &d_items, &d_status, &d_descs, &d_heavy, &d_ritems, &d_rstatus}) release(*b);
+  for (DevBuf *b : {&d_counters, &d_segs, &d_items, &d_status, &d_descs, &d_heavy, &d_ritems, &d_rstatus, &d_retry}) release(*b);
   if (ctr[CTR_ERR]) return fail(h, KC_ERR_OVERFLOW, "survivor output capacity exceeded");
   h->n_surv = ctr[CTR_SURV];
   h->n_pf = ctr[CTR_PF];

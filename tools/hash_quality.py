@@ -1,3 +1,6 @@
+"""Bucket statistics of the count stage's slot hash (kc_device.cuh: table_hash) against fmix64 (MurmurHash3's finaliser) on
+keys shaped like one partition: k-mers that share a minimizer at varying offsets, many of them one substitution apart.
+Prints (largest bucket, buckets over 4 entries, fingerprint collisions inside a bucket) for both. CPU only: python tools/hash_quality.py"""
 import numpy as np
 M64=np.uint64(0xFFFFFFFFFFFFFFFF)
 def mix(x):
