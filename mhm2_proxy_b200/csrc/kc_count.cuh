@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   __shared__ u64 s_obase[2];
   __shared__ u32 s_ocur[2];
   __shared__ __align__(16) WorkItem s_work;
-  __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed, s_widx, s_next;
+  __shared__ u32 s_nkeys, s_over, s_wide, s_live, s_prev, s_consumed, s_widx;
   __shared__ u32 warp_c[32], warp_p[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int grp = wid, gt = lane;  // pipeline = warp
@@ -152,9 +152,9 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const u32 nbuckets = a.tab_size >> 2;
   const u32 tab_s = (u32)__cvta_generic_to_shared(tab);
   const int nwb = a.nwb;
-  // supermers taken per chunk: what the staging buffer holds, and as many as will almost surely fit the instance list (a
-  // supermer has (w + 1) / 2 k-mers on average; the few chunks that do not fit run a second, short pass for the rest)
-  const int sup_per_chunk = max(1, min(min(GRP_THREADS, GRP_STAGE_MAX / rw), (2 * GRP_EXP * 4 / 5) / (a.w + 1)));
+  // supermers staged per chunk: what the staging buffer holds, and no more than the instance list will take (a supermer has
+  // (w + 1) / 2 k-mers on average; staging records that do not fit the list means staging them again)
+  const int sup_per_chunk = min(min(GRP_THREADS, GRP_STAGE_MAX / rw), 2 * GRP_EXP / (a.w + 1) + 3);
   u32 my_max_probe = 0;
   // Work items are dealt round-robin to the CTAs: first the heavy list (outlier partitions, heaviest first, so that none of
   // them starts last and becomes the tail), then every item in partition order, skipping the ones the heavy list covered.
@@ -211,21 +211,16 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       __syncthreads();
       if (s_over) break;
       if (tid < ns) segc[tid] = a.segs[it.seg_begin + sg0 + tid];
-      if (tid == 0) s_next = a.segs[it.seg_begin + sg0].sup0;
       __syncthreads();
-      const u32 r_hi = segc[ns - 1].sup0 + segc[ns - 1].nsup;
+      // every warp streams its own contiguous 1/32 of this round's supermers (handing chunks out from a shared cursor was
+      // measured and lost 4-8 %: v20)
+      const u32 r_lo = segc[0].sup0, r_hi = segc[ns - 1].sup0 + segc[ns - 1].nsup;
+      const u32 span = r_hi - r_lo;
+      const u32 g_lo = r_lo + (u32)(((u64)span * grp) / CNT_GROUPS), g_hi = r_lo + (u32)(((u64)span * (grp + 1)) / CNT_GROUPS);
+      u32 c0 = g_lo;
+      int seg_hint = 0;
+      while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
       u32 consumed = 0;
-      bool stop = false;
-      // the warps take the supermers of this round a chunk at a time from a shared cursor: a warp slowed down by claims or
-      // long probes simply takes fewer chunks, and the barrier at the end of the item waits for one chunk at most
-      while (!stop) {
-        u32 c0 = 0;
-        if (lane == 0) c0 = atomicAdd(&s_next, (u32)sup_per_chunk);
-        c0 = __shfl_sync(0xffffffffu, c0, 0);
-        if (c0 >= r_hi) break;
-        const u32 g_hi = min(c0 + (u32)sup_per_chunk, r_hi);
-        int seg_hint = 0;
-        while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
       while (c0 < g_hi) {
         // ---- a. one supermer record per thread: copy it to the staging buffer ----
         const u32 g = c0 + (u32)gt;
@@ -407,13 +402,12 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             atomicOr(v + VR + 2, 1u << (l * 5 + r));
           }
         }
-        stop = __any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0);  // also orders this chunk's reads of the staging
-                                                                        // buffer before the next chunk's writes
+        const bool stop = __any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0);  // also orders this chunk's reads of the
+                                                                                   // staging buffer before the next chunk's writes
         c0 += n_take;
         consumed += n_take;
         if (stop) break;
         while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
-      }
       }
       if (gt == 0 && consumed) atomicAdd(&s_consumed, consumed);
     }
@@ -444,7 +438,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       if ((over || wide_needed) && !a.measure_only) {
         const u64 slot = atomicAdd((unsigned long long *)&a.counters[CTR_RETRY], 1ull) - a.retry_base;
         if (a.retry) {
-          a.retry[slot].item = it;
+          a.retry[slot].item = a.items[item_idx];  // re-read: keeps the descriptor out of the registers of the hot loops
           a.retry[slot].st = st;
         }
       }
