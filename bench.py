@@ -163,7 +163,9 @@ def run_reference_arm(args):
 
 
 def workload_config(args, reads_per_gpu, n_gpus):
-    return {"workload": f"C2: ~{reads_per_gpu * READ_LEN / 1e9:.2f} Gbase synthetic 150bp paired reads per GPU, k={list(args.ks)}, "
+    tag = "C2" if (reads_per_gpu == C2_READS and tuple(args.ks) == tuple(C2_KS)) else \
+        "C3 (one GPU's eighth of 50 Gbase)" if (tuple(args.ks) == (31,) and reads_per_gpu >= 41_000_000) else "custom"
+    return {"workload": f"{tag}: ~{reads_per_gpu * READ_LEN / 1e9:.2f} Gbase synthetic 150bp paired reads per GPU, k={list(args.ks)}, "
                         f"kcount on {n_gpus}xB200", "reads_per_gpu": reads_per_gpu, "read_len": READ_LEN, "k": list(args.ks),
             "genome_bp": GENOME_BP, "n_genomes": N_GENOMES, "error_rate": ERR, "dmin_thres": 2,
             "l2_flush": "inputs (>= 2 GB) and supermer buffers are far larger than the 126 MB L2; nothing is reused across steps",
