@@ -14,4 +14,4 @@ for k in (21, 33):
         kc.finish()
         st = kc.stats()
         kc.close()
-    print(f"{os.environ.get('KCOUNT_B200_LIB', 'default')} k={k}: COUNT {st['ms_parse_count']:.2f} FILL {st['ms_parse_fill']:.2f} parse {st['ms_parse']:.2f} count_kernel {st['ms_insert']:.2f} finish {st['ms_finish']:.2f} items {st['num_partitions']} survivors {st['survivors']}", flush=True)
+    print(f"{os.environ.get('KCOUNT_B200_LIB', 'default')} k={k}: parse_kernel {st['ms_parse_count']:.2f} fill_kernel {st['ms_parse_fill']:.2f} parse {st['ms_parse']:.2f} count_kernel {st['ms_insert']:.2f} finish {st['ms_finish']:.2f} items {st['num_partitions']} survivors {st['survivors']}", flush=True)
