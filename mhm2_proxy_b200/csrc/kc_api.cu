@@ -1,6 +1,6 @@
 // Host side of the B200 kcount library and its C ABI (include/kcount_b200.h).
 // One handle = one shard (one GPU). Pipeline per handle:
-//   add_reads/add_contigs : [H2D copy] -> parse COUNT -> exact bucket layout -> parse FILL          (kc_parse.cuh)
+//   add_reads/add_contigs : [H2D copy] -> parse_kernel -> exact bucket layout -> fill_kernel   (kc_parse.cuh)
 //   finish                : [NCCL all-to-all of the per-shard bucket ranges] -> per group of partitions:
 //                           clear tables -> insert -> filter/compact                               (kc_count.cuh)
 // There is no CPU fallback: every data-path step is a CUDA kernel; host code only sizes, allocates and launches.
@@ -512,7 +512,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
 
   cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
   CK(cudaEventRecord(e0, h->s_main));
-  // COUNT
+  // parse_kernel: bucket histogram + supermer lists
   Block blk;
   blk.is_ctg = is_ctg;
   CK(dev_alloc((void **)&blk.d_hist, sizeof(BucketHist) * NP));
@@ -541,7 +541,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   const size_t rec_bytes = (size_t)hs * a.rw * 4;
   CK(dev_alloc((void **)&blk.rec, rec_bytes + 64));
   if (hs >> 32) return fail(h, KC_ERR_INVALID, "internal: %llu supermers in one batch do not fit the 32-bit bucket cursors", (unsigned long long)hs);
-  // FILL
+  // fill_kernel: records into the exact-size buckets
   a.cursor = (u32 *)h->d_cursor.p;
   {
     static const int hint = getenv("KC_FILL_L2_HINT") ? atoi(getenv("KC_FILL_L2_HINT")) : 1;  // A/B switch (tools/prof_run.py)

@@ -159,13 +159,13 @@ __global__ void meta_store_kernel(const MetaWords m, int n, u64 *dst) {
 }
 
 // One exchange round over NCCL. Collective, but NOT tied to a batch number: a shard calls it whenever it has a parsed
-// block to hand out (blk != null, from parse_batch right after FILL was launched) and, from kc_finish, with blk == null and
+// block to hand out (blk != null, from parse_batch right after the fill kernel was launched) and, from kc_finish, with blk == null and
 // done == true until every shard has said "done" in the same round. Round r of one shard pairs with round r of every
 // other shard, whatever each of them brought. Per round:
 //   1. all-gather of [done, is_ctg, P, nsup for each destination] (N+3 words per shard),
 //   2. one NCCL group on the comm stream: my directory slice (P entries) + my record range to every destination that gets
 //      something, and the matching receives. Between a pair of ranks the order is (directory, records).
-// The group is not waited for: it runs on s_comm behind the "FILL done" event while the main stream parses the next batch;
+// The group is not waited for: it runs on s_comm behind the "fill done" event while the main stream parses the next batch;
 // receives are turned into blocks in finish_exchange.
 int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
 #if KC_HAVE_NCCL_H
@@ -230,7 +230,7 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
   bool any_send = false;
   for (int d = 0; d < N; d++) any_send = any_send || mine[3 + d] != 0;
   if (inc.empty() && !any_send) return KC_OK;
-  if (any_send) CK(cudaStreamWaitEvent(st, h->ev_fill, 0));  // the records are being written by FILL on the main stream
+  if (any_send) CK(cudaStreamWaitEvent(st, h->ev_fill, 0));  // the records are being written by the fill kernel on the main stream
   NC(a.GroupStart());
   u64 sent = 0;
   for (int d = 0; d < N; d++) {

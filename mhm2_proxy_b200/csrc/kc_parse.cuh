@@ -29,7 +29,7 @@
 
 namespace kc {
 
-struct BucketHist {  // per bucket, per batch; bumped by ONE 64-bit RED in COUNT, nsup is the 32-bit cursor in FILL
+struct BucketHist {  // per bucket, per batch; bumped by ONE 64-bit RED per supermer in the parse kernel
   u32 nsup;   // supermers
   u32 ninst;  // k-mer instances
 };
