@@ -2,8 +2,8 @@
  *
  * This is the drop-in boundary: plain pointers and sizes, no C++/torch types, int status codes (0 = ok), no
  * exceptions. Every entry point names the reference interface it replaces (paths relative to the reference's src/).
- * The reference-side binding (kcount_b200.cpp implementing SeqBlockInserter<MAX_K>/HashTableInserter<MAX_K>) is in
- * INTEGRATION.md and mhm2_proxy_b200/csrc/kcount_b200_host.hpp.
+ * The reference-side binding (implementing SeqBlockInserter<MAX_K>/HashTableInserter<MAX_K> over this header) is
+ * integration/kcount_b200.cpp; INTEGRATION.md shows how it is added to the reference's build.
  *
  * Semantics = the reference CPU path (kcount/kcount_cpu.cpp), bit-exact: canonical k-mer, saturating u16 count,
  * chosen left/right extension char (A,C,G,T,F,X); 'N' packs as 'G' in k-mers and never counts as an extension; first
@@ -44,9 +44,7 @@ typedef struct kc_config {
                                   plays the role of estimate_num_kmers (contigging.cpp:61-91) */
   int32_t keep_prefilter;    /* 1 = also keep every distinct k-mer's counters after the reads pass (debug parity) */
   int32_t batch_reads;       /* 0 = auto. reads per internal batch (H2D copy / parse / exchange pipelining unit) */
-  int32_t dbg_key_cap;       /* 0 = auto (what fits in shared memory). Upper bound on the distinct k-mers one shared-memory
-                                table holds; tests set it small to force the sub-pass path (result-invariant) */
-  int32_t reserved[5];
+  int32_t reserved[6];
 } kc_config;
 
 /* counters the reference logs (kcount.cpp:93-97, kcount_cpu.cpp:107-112,467-487,525-527) */
@@ -63,22 +61,27 @@ typedef struct kc_stats {
   uint64_t distinct;            /* distinct canonical k-mers in this shard before the filter */
   uint64_t purged;              /* distinct - survivors */
   uint64_t survivors;
-  uint64_t dropped;             /* always 0: a partition that does not fit is re-run in sub-passes instead of dropping */
   uint64_t table_retries;       /* work items re-run (split into sub-passes, or with wide counters) */
   uint64_t max_probe;
   uint64_t num_partitions;
-  /* CUDA-event times on the library's own stream, summed over launches. ms_parse = parse_count + parse_fill kernels
-   * plus the bucket-layout round trip between them; ms_insert = the count kernel (insert + filter + compaction fused;
-   * ms_filter and ms_clear stay 0: the table lives in shared memory and is filtered where it was built). */
-  double ms_h2d, ms_parse, ms_exchange, ms_insert, ms_filter, ms_total;
-  double ms_parse_count, ms_parse_fill, ms_clear, ms_finish;
+  uint64_t supermer_bytes_recv; /* bytes of supermer records + directories received from other GPUs */
+  uint64_t exchange_rounds;     /* exchange rounds this shard took part in (data rounds + drain rounds) */
+  /* CUDA-event times on the library's own streams, summed over launches. ms_parse = parse + fill kernels plus the
+   * bucket-layout round trip between them; ms_insert = the count kernel (insert + filter + compaction fused: the table
+   * lives in shared memory and is filtered where it was built). ms_exchange = exchange time the main stream had to WAIT
+   * for (what the overlap with parsing did not hide); ms_comm = time the exchange groups occupied the communication
+   * stream (send + receive of supermer_bytes_sent / _recv: the figure NVLink GB/s is computed from). */
+  double ms_h2d, ms_parse, ms_exchange, ms_insert, ms_comm, ms_total;
+  double ms_parse_count, ms_parse_fill, ms_finish;
   uint64_t gpu_launches;        /* kernels launched by this handle so far */
-  uint64_t n_parse_launches, n_insert_launches, n_filter_launches;
+  uint64_t n_parse_launches, n_insert_launches;
   uint64_t table_bytes_max;     /* shared memory per CTA of the count kernel (index table + key store + staging) */
   uint64_t reserved[4];
 } kc_stats;
 
 void kc_config_default(kc_config *cfg, int32_t kmer_len);
+/* sizeof(kc_config) and sizeof(kc_stats) as the library was compiled: bindings in other languages check their mirrors */
+void kc_struct_sizes(uint32_t *config_bytes, uint32_t *stats_bytes);
 
 /* KmerDHT<MAX_K> ctor + HashTableInserter<MAX_K>::init (kmer_dht.cpp:105-154, kcount_cpu.cpp:425-443) */
 int kc_create(const kc_config *cfg, kc_handle **out);
@@ -127,9 +130,24 @@ int kc_add_reads_ascii(kc_handle *h, const char *seqs, const uint64_t *offsets, 
 int kc_set_dmin_thres(kc_handle *h, int32_t dmin_thres);
 
 /* multi-GPU: bind an NCCL communicator built from a 128-byte ncclUniqueId shared by all shards
- * (replaces ThreeTierAggrStore<Supermer> / rpc_ff, kmer_dht.cpp:133,146-149,222-231). Not needed when num_shards==1. */
+ * (replaces ThreeTierAggrStore<Supermer> / rpc_ff, kmer_dht.cpp:133,146-149,222-231). Not needed when num_shards==1.
+ * Collective discipline once a communicator is bound (it mirrors the reference's, SURVEY.md 8b "Threading"):
+ *   - kc_add_reads* / kc_add_contigs run one EXCHANGE ROUND per internal batch (an all-gather of sizes + one group of
+ *     sends/receives). Rounds pair up by index across shards, whatever each shard brought, so shards may add different
+ *     amounts of data in a different number of calls — but a shard inside an add call needs its peers to keep taking
+ *     rounds: between the last add of a phase and any OTHER collective or host barrier every shard must call kc_flush
+ *     (the reference has the same rule: SeqBlockInserter::done_processing -> flush_updates -> barrier, kcount.cpp:93-96,
+ *     kmer_dht.cpp:227-231). kc_finish flushes implicitly.
+ *   - kc_flush, kc_finish, kc_finish_to_host are collective. */
 int kc_comm_unique_id(uint8_t id128[128]);
 int kc_comm_init(kc_handle *h, const uint8_t id128[128]);
+/* KmerDHT::flush_updates (kmer_dht.cpp:227-231): collective. Takes part in exchange rounds until EVERY shard has called
+ * kc_flush (or kc_finish); when it returns no shard is inside a round and everything sent so far has been received.
+ * No-op for num_shards == 1. */
+int kc_flush(kc_handle *h);
+/* number of CUDA devices visible to this process (the binding's default device is rank_me() % this, as the reference's
+ * gpu_utils.cpp:68-75 does) */
+int kc_device_count(int32_t *n);
 
 /* several shards inside ONE process (handles[i] = shard i of n, any devices): exchange by peer copies, then finish all.
  * Same role as kc_comm_init + kc_finish on every rank; used by tests and by single-process multi-GPU drivers. */
@@ -154,6 +172,13 @@ int kc_copy_survivors(kc_handle *h, uint64_t *kmer_words, uint16_t *counts, char
  * Line order is unspecified (the reference iterates a hash map). */
 int kc_dump_kmers(kc_handle *h, const char *path);
 
+/* Order-independent digest of this shard's surviving table, computed on the device: out4 = {n, sum of counts,
+ * sum over rows of mix(row) mod 2^64, xor over rows of mix(row)} with mix(row): x = 0x9E3779B97F4A7C15; for every key word
+ * w: x = fmix64(x ^ w); x = fmix64(x ^ (count | left << 16 | right << 24)) (fmix64 = MurmurHash3's finaliser,
+ * hash_funcs.c:65-74). Two tables are equal iff (with overwhelming probability) their digests are: bench.py compares it with
+ * the same digest of the reference's local_kmers at full workload size. */
+int kc_table_digest(kc_handle *h, uint64_t out4[4]);
+
 /* device-resident view of the same arrays (valid until kc_destroy) */
 int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,
                         const char **d_right);
@@ -163,6 +188,10 @@ int kc_num_prefilter(kc_handle *h, uint64_t *n);
 int kc_copy_prefilter(kc_handle *h, uint64_t *kmer_words, uint16_t *vals9);
 
 int kc_get_stats(kc_handle *h, kc_stats *st);
+
+/* test knob, not part of the product interface: upper bound on the distinct k-mers one shared-memory table holds
+ * (0 = what fits), to force the sub-pass path on small inputs; result-invariant. Call before the first add. */
+int kc_debug_set_key_cap(kc_handle *h, int32_t key_cap);
 
 /* ---- primitives, exported for known-answer tests of the device code (each runs a tiny kernel) ----
  * kmers: n ASCII k-mers of length k back to back. Outputs per k-mer: words[N_LONGS], rc_words[N_LONGS],

@@ -113,6 +113,10 @@ template <int MAX_K>
 void SeqBlockInserter<MAX_K>::done_processing(dist_object<KmerDHT<MAX_K>> &kmer_dht) {
   (void)kmer_dht;
   flush_block<MAX_K>(state);
+  // ranks stage different numbers of batches; every batch is one exchange round inside the library. kc_flush keeps this
+  // rank taking (empty) rounds until every rank is done adding, so no rank waits in a round while a peer sits in the
+  // reductions and barriers that follow (kcount.cpp:93-96, kmer_dht.cpp:227-231)
+  if (auto &round = B200Round<MAX_K>::get(); round.h) die_on(round.h, kc_flush(round.h), "kc_flush");
   auto tot_kmers = reduce_one(state->num_kmers, op_fast_add, 0).wait();
   SLOG_VERBOSE("Processed a total of ", tot_kmers, " kmers\n");  // kcount_cpu.cpp:107-112
 }
@@ -146,9 +150,11 @@ void HashTableInserter<MAX_K>::init(int num_elems, bool use_qf) {
   cfg.dmin_thres = _dmin_thres;  // set by analyze_kmers before count_kmers runs (kcount.cpp:145); re-read at finish
   cfg.num_shards = rank_n();     // the table is sharded exactly as the UPC++ ranks shard it (kmer_dht.cpp:192-196)
   cfg.shard_id = rank_me();
-  int ndev = 1;
-  // one rank per GPU of the node, as the reference does (gpu_utils.cpp:68-75: rank % device count)
-  if (const char *e = getenv("KCOUNT_B200_DEVICES")) ndev = max(1, atoi(e));
+  // one rank per GPU of the node, as the reference does (gpu_utils.cpp:68-75: rank % device count);
+  // KCOUNT_B200_DEVICES restricts the ranks to the first n devices
+  int32_t ndev = 1;
+  if (kc_device_count(&ndev) != KC_OK || ndev < 1) DIE("kcount_b200: no CUDA device");
+  if (const char *e = getenv("KCOUNT_B200_DEVICES")) ndev = max(1, min((int)ndev, atoi(e)));
   cfg.device = local_team().rank_me() % ndev;
   // num_elems = KmerDHT's my_num_kmers = estimate_num_kmers's instances per rank (contigging.cpp:61-91, kmer_dht.cpp:152);
   // every rank passes the same reduce_all'ed value, so every shard derives the same partition count
@@ -211,7 +217,8 @@ void HashTableInserter<MAX_K>::insert_into_local_hashtable(dist_object<KmerMap<M
   auto tot_surv = reduce_one(st.survivors, op_fast_add, 0).wait();
   auto max_surv = reduce_one(st.survivors, op_fast_max, 0).wait();
   SLOG_VERBOSE("B200 kcount: ", tot_distinct, " distinct kmers, purged ", perc_str(tot_purged, tot_distinct), ", kept ", tot_surv,
-               " (avg per rank ", tot_surv / rank_n(), ", max ", max_surv, "); dropped 0\n");  // kcount_cpu.cpp:467-487,525-527
+               " (avg per rank ", tot_surv / rank_n(), ", max ", max_surv, "); nothing dropped (", st.table_retries,
+               " partitions re-run in sub-passes)\n");  // kcount_cpu.cpp:467-487,525-527
 }
 
 // explicit instantiations for every MAX_K the tree is built for, as kcount_cpu.cpp:533-555 does
@@ -233,8 +240,7 @@ SEQ_BLOCK_INSERTER_K(128);
 HASH_TABLE_INSERTER_K(128);
 #endif
 #if MAX_BUILD_KMER >= 160
-SEQ_BLOCK_INSERTER_K(160);
-HASH_TABLE_INSERTER_K(160);
+#error "kcount_b200 supports k <= 127 (MAX_BUILD_KMER <= 128): libkcount_b200.so rejects longer k-mers"
 #endif
 #undef SEQ_BLOCK_INSERTER_K
 #undef HASH_TABLE_INSERTER_K

@@ -63,6 +63,9 @@ struct kc_handle {
   u32 P = 0;  // buckets per shard the parse stage uses (0 until the first add decides)
   bool auto_merge = false;  // P was chosen by the library: fine-grained, neighbours are merged into work items at finish
   bool finished = false, has_ctg = false;
+  bool phase_open = true;   // multi-shard: this shard has added data (or never flushed) since its last drain of exchange rounds
+  int dbg_key_cap = 0;      // kc_debug_set_key_cap
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> comm_ev;  // one pair around every exchange group on s_comm (ms_comm)
   cudaStream_t s_main = nullptr, s_copy = nullptr, s_comm = nullptr;
   std::vector<Pending> pending;
   DevBuf d_meta, d_meta_all, d_tot, d_scan, d_scan_comm;
@@ -230,6 +233,11 @@ extern "C" void kc_config_default(kc_config *cfg, int32_t kmer_len) {
   cfg->device = 0;
 }
 
+extern "C" void kc_struct_sizes(uint32_t *config_bytes, uint32_t *stats_bytes) {
+  if (config_bytes) *config_bytes = (uint32_t)sizeof(kc_config);
+  if (stats_bytes) *stats_bytes = (uint32_t)sizeof(kc_stats);
+}
+
 extern "C" const char *kc_last_error(const kc_handle *h) { return h ? h->err.c_str() : "null handle"; }
 
 namespace {
@@ -328,7 +336,7 @@ void table_geometry(const kc_handle *h, bool wide, bool ctg, u32 &tab_size, u32 
   u64 cap = budget > fixed ? (budget - fixed) / per_key : 16;
   cap = std::min<u64>(cap, IDX_MASK - 1);
   (void)ctg;
-  if (h->cfg.dbg_key_cap > 0) cap = std::min<u64>(cap, (u64)h->cfg.dbg_key_cap);
+  if (h->dbg_key_cap > 0) cap = std::min<u64>(cap, (u64)h->dbg_key_cap);
   cap = std::max<u64>(cap, 16);
   key_cap = (u32)cap;
   tab_size = (u32)((2 * cap + 15) & ~15ull);  // whole 16-byte buckets; keeps what follows 16-byte aligned
@@ -558,6 +566,7 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   CK(cudaEventRecord(e1, h->s_main));
   CK(cudaEventRecord(h->ev_fill, h->s_main));
   if (h->comm) {  // multi-shard with NCCL: this batch's supermers leave now, while the next batch is copied in and parsed
+    h->phase_open = true;
     int rcx = exchange_round(h, &blk, false, nullptr);
     if (rcx) return rcx;
   }
@@ -1545,6 +1554,71 @@ extern "C" int kc_dump_kmers(kc_handle *h, const char *path) {
   return rc;
 }
 
+namespace {
+// kc_table_digest: order-independent digest of the surviving table (include/kcount_b200.h)
+__global__ void __launch_bounds__(256) digest_kernel(const u64 *keys, const uint16_t *counts, const char *left, const char *right, u64 n,
+                                                     int KW, u64 *out4) {
+  u64 sc = 0, sm = 0, xm = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+    u64 x = 0x9E3779B97F4A7C15ULL;
+    for (int j = 0; j < KW; j++) x = fmix64(x ^ keys[i * KW + j]);
+    const u64 c = counts[i];
+    x = fmix64(x ^ (c | ((u64)(unsigned char)left[i] << 16) | ((u64)(unsigned char)right[i] << 24)));
+    sc += c;
+    sm += x;
+    xm ^= x;
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) {
+    sc += __shfl_xor_sync(0xffffffffu, sc, d);
+    sm += __shfl_xor_sync(0xffffffffu, sm, d);
+    xm ^= __shfl_xor_sync(0xffffffffu, xm, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd((unsigned long long *)&out4[1], sc);
+    atomicAdd((unsigned long long *)&out4[2], sm);
+    atomicXor((unsigned long long *)&out4[3], xm);
+  }
+}
+}  // namespace
+
+extern "C" int kc_table_digest(kc_handle *h, uint64_t out4[4]) {
+  if (!h || !out4) return KC_ERR_INVALID;
+  if (!h->finished) return fail(h, KC_ERR_STATE, "not finished");
+  CK(cudaSetDevice(h->cfg.device));
+  DevBuf d;
+  RC(ensure(h, d, 32));
+  CK(cudaMemsetAsync(d.p, 0, 32, h->s_main));
+  const u64 n = h->n_surv;
+  if (n) {
+    const unsigned grid = (unsigned)std::min<u64>((n + 255) / 256, (u64)h->sms * 8);
+    digest_kernel<<<grid, 256, 0, h->s_main>>>((const u64 *)h->out_keys.p, (const uint16_t *)h->out_counts.p, (const char *)h->out_left.p,
+                                               (const char *)h->out_right.p, n, h->KW, (u64 *)d.p);
+    h->st.gpu_launches++;
+    CK(cudaGetLastError());
+  }
+  CK(cudaMemcpyAsync(out4, d.p, 32, cudaMemcpyDeviceToHost, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
+  out4[0] = n;
+  release(d);
+  return KC_OK;
+}
+
+extern "C" int kc_device_count(int32_t *n) {
+  if (!n) return KC_ERR_INVALID;
+  int c = 0;
+  if (cudaGetDeviceCount(&c) != cudaSuccess) return KC_ERR_CUDA;
+  *n = c;
+  return KC_OK;
+}
+
+extern "C" int kc_debug_set_key_cap(kc_handle *h, int32_t key_cap) {
+  if (!h || key_cap < 0) return KC_ERR_INVALID;
+  if (h->P) return fail(h, KC_ERR_STATE, "kc_debug_set_key_cap after the first add");
+  h->dbg_key_cap = key_cap;
+  return KC_OK;
+}
+
 extern "C" int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,
                                    const char **d_right) {
   if (!h) return KC_ERR_INVALID;
@@ -1632,6 +1706,7 @@ extern "C" int kc_destroy(kc_handle *h) {
   for (auto e : h->ev_chunk) cudaEventDestroy(e);
   if (h->ev_x0) cudaEventDestroy(h->ev_x0);
   if (h->ev_x1) cudaEventDestroy(h->ev_x1);
+  for (auto &pr : h->comm_ev) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   void kc_comm_destroy(kc_handle *);
   kc_comm_destroy(h);
   delete h;

@@ -138,6 +138,28 @@ extern "C" int kc_comm_init(kc_handle *h, const uint8_t id128[128]) {
     it = comm_cache().emplace(key, c).first;
   }
   h->comm = it->second;
+  // Shards must bucket with the same number of partitions. Agree once, here: the largest instance hint of any shard sizes
+  // the partitions of all of them (an explicit num_partitions must already be equal everywhere). Shards that give no hint
+  // at all still work when their first adds are of similar size; otherwise the first exchange round reports the mismatch.
+  {
+    const int N = h->cfg.num_shards;
+    RC(ensure(h, h->d_meta, 16));
+    RC(ensure(h, h->d_meta_all, 16 * (size_t)N));
+    u64 mine[2] = {(u64)h->cfg.num_partitions, h->cfg.expected_instances};
+    std::vector<u64> all(2 * (size_t)N);
+    CK(cudaMemcpyAsync(h->d_meta.p, mine, 16, cudaMemcpyHostToDevice, h->s_comm));
+    NC(a.AllGather(h->d_meta.p, h->d_meta_all.p, 2, ncclUint64, h->comm->comm, h->s_comm));
+    CK(cudaMemcpyAsync(all.data(), h->d_meta_all.p, 16 * (size_t)N, cudaMemcpyDeviceToHost, h->s_comm));
+    CK(cudaStreamSynchronize(h->s_comm));
+    u64 hint = 0;
+    for (int r = 0; r < N; r++) {
+      if (all[2 * r] != mine[0])
+        return fail(h, KC_ERR_INVALID, "shards disagree on cfg.num_partitions (%llu here, %llu on shard %d)", (unsigned long long)mine[0],
+                    (unsigned long long)all[2 * r], r);
+      hint = std::max(hint, all[2 * r + 1]);
+    }
+    h->cfg.expected_instances = hint;
+  }
   return KC_OK;
 #else
   return fail(h, KC_ERR_COMM, "built without nccl.h");
@@ -179,7 +201,7 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
   std::vector<u64> mine(MW, 0);
   mine[0] = done ? 1 : 0;
   mine[1] = blk && blk->is_ctg ? 1 : 0;
-  mine[2] = h->P;
+  mine[2] = (u64)h->P | ((u64)(h->auto_merge ? 1 : 0) << 32);
   if (blk && blk->tot_sup)
     for (int d = 0; d < N; d++)
       if (d != me) mine[3 + d] = blk->dest_base[d + 1] - blk->dest_base[d];
@@ -199,9 +221,11 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
   const u64 *all = h_all;
   bool everyone = true;
   u64 P = h->P;
+  h->st.exchange_rounds++;
   for (int r = 0; r < N; r++) {
     everyone = everyone && all[r * MW] != 0;
-    const u64 pr = all[r * MW + 2];
+    const u64 pr = all[r * MW + 2] & 0xFFFFFFFFull;
+    if (pr && !h->P && !P) h->auto_merge = (all[r * MW + 2] >> 32) != 0;  // adopted geometry: merge neighbours like the peers do
     if (pr && !P) P = pr;
     if (pr && pr != P)
       return fail(h, KC_ERR_INVALID, "shards disagree on num_partitions (%llu vs %llu): set cfg.num_partitions or expected_instances",
@@ -231,8 +255,12 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
   for (int d = 0; d < N; d++) any_send = any_send || mine[3 + d] != 0;
   if (inc.empty() && !any_send) return KC_OK;
   if (any_send) CK(cudaStreamWaitEvent(st, h->ev_fill, 0));  // the records are being written by the fill kernel on the main stream
+  std::pair<cudaEvent_t, cudaEvent_t> ev;  // what the group occupies on the communication stream: ms_comm
+  CK(cudaEventCreate(&ev.first));
+  CK(cudaEventCreate(&ev.second));
+  CK(cudaEventRecord(ev.first, st));
   NC(a.GroupStart());
-  u64 sent = 0;
+  u64 sent = 0, recvd = 0;
   for (int d = 0; d < N; d++) {
     const u64 nsup = mine[3 + d];
     if (!nsup) continue;
@@ -243,10 +271,14 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
   for (auto &in : inc) {
     NC(a.Recv(in.p.dir, sizeof(BucketHist) * P, ncclUint8, in.src, h->comm->comm, st));
     NC(a.Recv(in.p.rec, RB * in.p.nsup, ncclUint8, in.src, h->comm->comm, st));
+    recvd += sizeof(BucketHist) * P + RB * in.p.nsup;
   }
   NC(a.GroupEnd());
+  CK(cudaEventRecord(ev.second, st));
+  h->comm_ev.push_back(ev);
   for (auto &in : inc) h->pending.push_back(in.p);
   h->st.supermer_bytes_sent += sent;
+  h->st.supermer_bytes_recv += recvd;
   return KC_OK;
 #else
   (void)blk; (void)done; (void)all_done;
@@ -258,11 +290,34 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
 
 // NCCL transport, the part that runs in kc_finish: empty rounds until every shard is done, then the receives become blocks.
 // ms_exchange is the exchange time the count phase actually waits for (what the per-batch rounds did not hide).
+namespace {
+// drain: empty "done" rounds until every shard has said done in the same round. Every shard leaves at the same round index,
+// so the next phase (contigs after reads, kcount.cpp:148-150) starts with the rounds paired up again.
+int comm_drain(kc_handle *h) {
+  for (bool all_done = false; !all_done;) RC(exchange_round(h, nullptr, true, &all_done));
+  h->phase_open = false;
+  return KC_OK;
+}
+}  // namespace
+
+extern "C" int kc_flush(kc_handle *h) {
+  if (!h) return KC_ERR_INVALID;
+  if (h->finished) return fail(h, KC_ERR_STATE, "flush after finish");
+  if (h->cfg.num_shards < 2) return KC_OK;
+#if KC_HAVE_NCCL_H
+  if (!h->comm) return fail(h, KC_ERR_COMM, "multi-shard handle without a communicator: call kc_comm_init first");
+  CK(cudaSetDevice(h->cfg.device));
+  return comm_drain(h);
+#else
+  return fail(h, KC_ERR_COMM, "built without nccl.h");
+#endif
+}
+
 int kc_exchange(kc_handle *h) {
 #if KC_HAVE_NCCL_H
   if (!h->comm) return fail(h, KC_ERR_COMM, "multi-shard handle without a communicator: call kc_comm_init first");
   CK(cudaEventRecord(h->ev_x0, h->s_main));  // the main stream is idle here: x0..x1 is what kc_finish waits for
-  for (bool all_done = false; !all_done;) RC(exchange_round(h, nullptr, true, &all_done));
+  if (h->phase_open) RC(comm_drain(h));  // a shard that flushed and added nothing since has already taken its last round
   if (!h->P) decide_partitions(h, 0);
   for (auto &pd : h->pending) RC(make_rblock(h, pd.dir, pd.rec, pd.nsup, pd.is_ctg, h->s_comm));
   h->pending.clear();
@@ -272,6 +327,12 @@ int kc_exchange(kc_handle *h) {
   CK(cudaStreamSynchronize(h->s_main));
   CK(cudaStreamSynchronize(h->s_comm));
   h->st.ms_exchange += elapsed(h->ev_x0, h->ev_x1);
+  for (auto &pr : h->comm_ev) {
+    h->st.ms_comm += elapsed(pr.first, pr.second);
+    cudaEventDestroy(pr.first);
+    cudaEventDestroy(pr.second);
+  }
+  h->comm_ev.clear();
   return KC_OK;
 #else
   return fail(h, KC_ERR_COMM, "built without nccl.h");

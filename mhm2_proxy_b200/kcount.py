@@ -20,18 +20,18 @@ class KcConfig(C.Structure):
         ("kmer_len", C.c_int32), ("qual_cutoff", C.c_int32), ("dmin_thres", C.c_int32), ("dyn_min_depth", C.c_double),
         ("num_shards", C.c_int32), ("shard_id", C.c_int32), ("device", C.c_int32), ("num_partitions", C.c_int32),
         ("expected_instances", C.c_uint64), ("keep_prefilter", C.c_int32), ("batch_reads", C.c_int32),
-        ("dbg_key_cap", C.c_int32), ("reserved", C.c_int32 * 5),
+        ("reserved", C.c_int32 * 6),
     ]
 
 
 class KcStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "num_seqs", "num_bases", "instances_parsed", "instances_inserted", "ctg_instances_inserted", "supermers_out",
-        "supermer_bytes_out", "supermer_bytes_sent", "supermers_in", "distinct", "purged", "survivors", "dropped",
-        "table_retries", "max_probe", "num_partitions")] + [(n, C.c_double) for n in (
-            "ms_h2d", "ms_parse", "ms_exchange", "ms_insert", "ms_filter", "ms_total", "ms_parse_count", "ms_parse_fill",
-            "ms_clear", "ms_finish")] + [(n, C.c_uint64) for n in (
-                "gpu_launches", "n_parse_launches", "n_insert_launches", "n_filter_launches", "table_bytes_max")] + [
+        "supermer_bytes_out", "supermer_bytes_sent", "supermers_in", "distinct", "purged", "survivors",
+        "table_retries", "max_probe", "num_partitions", "supermer_bytes_recv", "exchange_rounds")] + [(n, C.c_double) for n in (
+            "ms_h2d", "ms_parse", "ms_exchange", "ms_insert", "ms_comm", "ms_total", "ms_parse_count", "ms_parse_fill",
+            "ms_finish")] + [(n, C.c_uint64) for n in (
+                "gpu_launches", "n_parse_launches", "n_insert_launches", "table_bytes_max")] + [
                     ("reserved", C.c_uint64 * 4)]
 
 
@@ -39,6 +39,7 @@ EXPORTS = [
     "kc_config_default", "kc_create", "kc_destroy", "kc_last_error", "kc_release_cached_memory", "kc_add_reads", "kc_add_reads_device", "kc_reads_create", "kc_reads_create_fastq", "kc_reads_copy_packed", "kc_add_reads_resident", "kc_reads_destroy", "kc_dump_kmers", "kc_add_reads_ascii", "kc_add_contigs", "kc_set_dmin_thres",
     "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_to_host", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
+    "kc_flush", "kc_device_count", "kc_table_digest", "kc_debug_set_key_cap", "kc_struct_sizes",
 ]
 
 _lib = None
@@ -84,6 +85,17 @@ def load_library():
     lib.kc_get_stats.argtypes = [vp, C.POINTER(KcStats)]
     lib.kc_prim_kmers.argtypes = [i32, i32, C.c_char_p, u64, i32, vp, vp, vp, vp, vp]
     lib.kc_prim_get_ext.argtypes = [i32, vp, u64, i32, C.c_double, vp]
+    lib.kc_flush.argtypes = [vp]
+    lib.kc_device_count.argtypes = [C.POINTER(i32)]
+    lib.kc_table_digest.argtypes = [vp, vp]
+    lib.kc_debug_set_key_cap.argtypes = [vp, i32]
+    lib.kc_struct_sizes.argtypes = [C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    lib.kc_struct_sizes.restype = None
+    a, b = C.c_uint32(), C.c_uint32()
+    lib.kc_struct_sizes(C.byref(a), C.byref(b))
+    if (a.value, b.value) != (C.sizeof(KcConfig), C.sizeof(KcStats)):
+        raise RuntimeError(f"{LIB_PATH}: struct sizes {a.value}/{b.value} differ from this binding's {C.sizeof(KcConfig)}/"
+                           f"{C.sizeof(KcStats)} (stale build?)")
     _lib = lib
     return lib
 
@@ -108,7 +120,7 @@ class KmerCounter:
         self.lib.kc_config_default(C.byref(cfg), kmer_len)
         cfg.dmin_thres, cfg.num_shards, cfg.shard_id, cfg.device = dmin_thres, num_shards, shard_id, device
         cfg.num_partitions, cfg.expected_instances = num_partitions, expected_instances
-        cfg.keep_prefilter, cfg.batch_reads, cfg.dbg_key_cap = int(keep_prefilter), batch_reads, dbg_key_cap
+        cfg.keep_prefilter, cfg.batch_reads = int(keep_prefilter), batch_reads
         cfg.qual_cutoff, cfg.dyn_min_depth = qual_cutoff, dyn_min_depth
         self.k = kmer_len
         self.n_longs = kmer_len // 32 + 1
@@ -120,6 +132,8 @@ class KmerCounter:
                 self.lib.kc_destroy(self.h)
                 self.h = None
             raise KcountError(f"kc_create failed ({ERR_NAMES.get(rc, rc)}): {msg}")
+        if dbg_key_cap:
+            self._ck(self.lib.kc_debug_set_key_cap(self.h, dbg_key_cap), "kc_debug_set_key_cap")
 
     def _ck(self, rc, what):
         if rc != KC_OK:
@@ -168,8 +182,18 @@ class KmerCounter:
             raise KcountError(f"kc_comm_unique_id failed ({ERR_NAMES.get(rc, rc)})")
         return bytes(buf)
 
+    def flush(self):
+        """KmerDHT::flush_updates: collective; drains the exchange rounds of the adds so far (no-op on one shard)."""
+        self._ck(self.lib.kc_flush(self.h), "kc_flush")
+
     def finish(self):
         self._ck(self.lib.kc_finish(self.h), "kc_finish")
+
+    def digest(self):
+        """kc_table_digest: (n, sum of counts, sum of row hashes mod 2^64, xor of row hashes) of this shard's table."""
+        out = np.zeros(4, dtype=np.uint64)
+        self._ck(self.lib.kc_table_digest(self.h, _ptr(out)), "kc_table_digest")
+        return tuple(int(x) for x in out)
 
     def dump_kmers(self, path):
         """KmerDHT::dump_kmers: "KMER count left right" per surviving k-mer; .gz -> gzip."""
@@ -305,6 +329,35 @@ class ResidentReads:
 
     def __exit__(self, *a):
         self.close()
+
+
+def _fmix64(x):
+    x = x ^ (x >> np.uint64(33))
+    x = x * np.uint64(0xff51afd7ed558ccd)
+    x = x ^ (x >> np.uint64(33))
+    x = x * np.uint64(0xc4ceb9fe1a85ec53)
+    return x ^ (x >> np.uint64(33))
+
+
+def table_digest(keys, counts, left, right):
+    """The digest kc_table_digest computes on the device, for a table held in numpy arrays (any row order)."""
+    keys = np.asarray(keys, dtype=np.uint64).reshape(len(counts), -1)
+    with np.errstate(over="ignore"):
+        x = np.full(len(counts), 0x9E3779B97F4A7C15, dtype=np.uint64)
+        for j in range(keys.shape[1]):
+            x = _fmix64(x ^ keys[:, j])
+        c = np.asarray(counts).astype(np.uint64)
+        x = _fmix64(x ^ (c | (np.asarray(left).astype(np.uint64) << np.uint64(16)) | (np.asarray(right).astype(np.uint64) << np.uint64(24))))
+        sm = int(x.sum(dtype=np.uint64)) if len(x) else 0
+    return (len(counts), int(c.sum()), sm, int(np.bitwise_xor.reduce(x)) if len(x) else 0)
+
+
+def device_count():
+    n = C.c_int32()
+    rc = load_library().kc_device_count(C.byref(n))
+    if rc != KC_OK:
+        raise KcountError(f"kc_device_count failed ({ERR_NAMES.get(rc, rc)})")
+    return n.value
 
 
 def finish_local_group(counters):

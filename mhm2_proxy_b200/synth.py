@@ -126,3 +126,84 @@ def count_instances(offsets, k):
     """Number of counted k-mer instances: sum over sequences of max(0, len - k - 1) (kcount_cpu.cpp:84-102,319)."""
     lens = np.diff(np.asarray(offsets).astype(np.int64))
     return int(np.maximum(lens - k - 1, 0).sum())
+
+
+def make_contig_tiling(community, k, seed=3, min_len=500, max_len=50000, depth_lo=2, depth_hi=200, dup_frac=0.02,
+                       conflict_frac=0.01, revcomp_frac=0.3):
+    """BASELINE config C4's stand-in for the previous round's uutigs: the true genomes cut end to end into
+    pieces of min_len..max_len bases with integer depths depth_lo..depth_hi; a few pieces are repeated (exact duplicates
+    and overlapping tails: same k-mers from several contigs) and a few carry one substituted base (k-mers whose extensions
+    disagree: the purge rules of kcount_cpu.cpp:356-406); some are reverse-complemented.
+    Returns ASCII bytes, offsets (uint64[n+1]), depths (float64)."""
+    codes, starts, _ = community
+    rng = np.random.default_rng(seed)
+    lut = np.frombuffer(b"ACGT", dtype=np.uint8)
+    cuts = []
+    for g in range(len(starts) - 1):
+        p, end = int(starts[g]), int(starts[g + 1])
+        while p < end:
+            ln = int(rng.integers(min_len, max_len + 1))
+            if end - (p + ln) < min_len:
+                ln = end - p
+            cuts.append((p, p + ln))
+            p += ln
+    n0 = len(cuts)
+    for _ in range(int(n0 * dup_frac)):
+        a, b = cuts[int(rng.integers(0, n0))]
+        if rng.random() < 0.5 and b - a > 2 * (k + 4):
+            a += int(rng.integers(1, b - a - k - 3))
+        cuts.append((a, b))
+    lens = np.array([b - a for a, b in cuts], dtype=np.int64)
+    offs = np.zeros(len(cuts) + 1, dtype=np.uint64)
+    offs[1:] = np.cumsum(lens).astype(np.uint64)
+    data = np.empty(int(offs[-1]), dtype=np.uint8)
+    flip = rng.random(len(cuts)) < revcomp_frac
+    mutate = rng.random(len(cuts)) < conflict_frac
+    for i, (a, b) in enumerate(cuts):
+        s = codes[a:b]
+        if mutate[i] and i >= n0:  # only repeated pieces: the original piece keeps the true base, the copy disagrees
+            s = s.copy()
+            j = int(rng.integers(0, len(s)))
+            s[j] = (s[j] + 1) & 3
+        if flip[i]:
+            s = (3 - s)[::-1]
+        data[int(offs[i]):int(offs[i + 1])] = lut[s]
+    depths = rng.integers(depth_lo, depth_hi + 1, size=len(cuts)).astype(np.float64)
+    return data, offs, depths
+
+
+def make_skewed_reads(n_reads, community, read_len=150, error_rate=0.01, seed=1, repeat_frac=0.001, repeat_len=2000,
+                      polya_frac=0.0002, out=None):
+    """BASELINE config C5: reads of a Zipf community, plus repeat_frac of the reads from one short repeat
+    (k-mers hundreds of times above the mean) and polya_frac poly-A reads with one variable base (ONE k-mer and a handful of
+    neighbours seen > 65535 times: saturating counters, heavy-hitter partitions). The special reads are spread evenly through
+    the set. Same output as make_reads."""
+    n_rep = int(n_reads * repeat_frac) & ~1
+    n_pa = int(n_reads * polya_frac)
+    n_main = n_reads - n_rep - n_pa
+    total = n_reads * read_len
+    data = out if out is not None else np.empty(total, dtype=np.uint8)
+    rows = data[:total].reshape(n_reads, read_len)
+    is_special = np.zeros(n_reads, dtype=bool)
+    n_sp = n_rep + n_pa
+    if n_sp:
+        is_special[np.linspace(0, n_reads - 1, n_sp).astype(np.int64)] = True
+        n_sp = int(is_special.sum())  # linspace may repeat an index for tiny inputs
+        n_pa = min(n_pa, n_sp)
+        n_rep = n_sp - n_pa
+        n_main = n_reads - n_sp
+    main, _ = make_reads(n_main, community, read_len=read_len, error_rate=error_rate, seed=seed)
+    rows[~is_special] = main.reshape(n_main, read_len)
+    sp = np.empty((n_sp, read_len), dtype=np.uint8)
+    if n_rep:
+        rep = make_community(repeat_len, n_genomes=1, seed=seed + 101)
+        r, _ = make_reads(n_rep, rep, read_len=read_len, error_rate=error_rate, seed=seed + 102)
+        sp[:n_rep] = r.reshape(n_rep, read_len)
+    if n_pa:
+        pa = np.full((n_pa, read_len), 0 | (31 << 3), dtype=np.uint8)
+        pa[:, read_len // 2] = (np.arange(n_pa) % 4) | (31 << 3)
+        sp[n_rep:] = pa
+    rng = np.random.default_rng(seed + 103)
+    rows[is_special] = sp[rng.permutation(n_sp)]
+    offsets = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(read_len)
+    return data[:total], offsets

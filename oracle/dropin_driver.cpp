@@ -7,13 +7,15 @@
 // analyze_kmers<MAX_K> on PackedReads + Contigs and reads kmer_dht->local_kmers, exactly what dbjg_traversal.cpp:301
 // consumes. Output: oracle/_ref/libkcount_dropin.so (git-ignored, links ../../mhm2_proxy_b200/libkcount_b200.so).
 //
-// The few PackedRead / PackedReads / Contigs members that kcount.cpp calls are restated below from packed_reads.cpp and
-// contigs.cpp (those translation units drag in the FASTQ reader and file layer, which are out of scope).
+// PackedRead / PackedReads are the reference's own packed_reads.cpp (compiled unmodified into _ref/packed_reads.o). The
+// three Contigs members that kcount.cpp calls are restated below from contigs.cpp:81-90 (that translation unit needs
+// upcxx-utils' dist_ofstream and the file layer, which are out of scope).
 #include <array>
 #include <algorithm>
 #include <bitset>
 #include <cassert>
 #include <cctype>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -57,62 +59,7 @@ size_t estimate_hashtable_memory(size_t num_elements, size_t element_size) {
   return expanded_num_elements * element_size;
 }
 
-// ---- packed_reads.cpp:66-72,91-159,178-207 restated: only what count_kmers touches ----
-PackedRead::PackedRead()
-    : read_id(0)
-    , read_len(0)
-    , bytes(nullptr) {}
-PackedRead::PackedRead(const PackedRead &copy)
-    : read_id(copy.read_id)
-    , read_len(copy.read_len)
-    , bytes(new unsigned char[read_len]) {
-  memcpy(bytes, copy.bytes, read_len);
-}
-PackedRead::PackedRead(PackedRead &&move)
-    : read_id(move.read_id)
-    , read_len(move.read_len)
-    , bytes(move.bytes) {
-  move.bytes = nullptr;
-  move.read_len = 0;
-}
-PackedRead::~PackedRead() { clear(); }
-void PackedRead::clear() {
-  if (bytes) delete[] bytes;
-  bytes = nullptr;
-  read_len = 0;
-  read_id = 0;
-}
-void PackedRead::unpack(string &read_id_str, string &seq, string &quals, int qual_offset) const {
-  char pair_id = (read_id < 0 ? '1' : '2');
-  read_id_str = "@r" + to_string(labs(read_id)) + '/' + pair_id;
-  seq.resize(read_len);
-  quals.resize(read_len);
-  for (int i = 0; i < read_len; i++) {
-    seq[i] = nucleotide_map[bytes[i] & 7];
-    quals[i] = qual_offset + (bytes[i] >> 3);
-  }
-}
-uint16_t PackedRead::get_read_len() { return read_len; }
-unsigned char *PackedRead::get_raw_bytes() { return bytes; }
-
-PackedReads::PackedReads(int qual_offset, vector<PackedRead> &new_packed_reads)
-    : packed_reads(new_packed_reads)
-    , index(0)
-    , qual_offset(qual_offset)
-    , fname("")
-    , str_ids(false) {
-  max_read_len = 0;
-  for (auto &packed_read : new_packed_reads) max_read_len = max((unsigned)packed_read.get_read_len(), max_read_len);
-}
-PackedReads::~PackedReads() {}
-bool PackedReads::get_next_read(string &id, string &seq, string &quals) {
-  if (index == packed_reads.size()) return false;
-  packed_reads[index].unpack(id, seq, quals, qual_offset);
-  index++;
-  return true;
-}
-void PackedReads::reset() { index = 0; }
-int64_t PackedReads::get_local_num_reads() { return packed_reads.size(); }
+// PackedRead / PackedReads: the reference's own packed_reads.cpp, compiled where it lies into _ref/packed_reads.o (Makefile)
 
 // ---- contigs.cpp:81-90 restated ----
 void Contigs::clear() {
@@ -126,6 +73,8 @@ namespace {
 
 struct Result {
   int n_longs = 0;
+  uint64_t n_local = 0;
+  double t_analyze = 0;  // wall seconds inside the reference's analyze_kmers (reads in PackedReads -> local_kmers filled)
   std::vector<uint64_t> keys;
   std::vector<uint16_t> counts;
   std::vector<char> left, right;
@@ -133,7 +82,7 @@ struct Result {
 
 template <int MAX_K>
 int run(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, const uint64_t *offs, uint64_t n_reads, const char *cseqs,
-        const uint64_t *coffs, const double *cdepths, uint64_t n_ctgs, Result *res) {
+        const uint64_t *coffs, const double *cdepths, uint64_t n_ctgs, Result *res, bool want_rows = true) {
   Kmer<MAX_K>::set_k(k);
   upcxx::shim_state::nranks() = 1;
   upcxx::shim_state::me() = 0;
@@ -161,7 +110,10 @@ int run(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, const uint
   {
     // contigging.cpp:115-118: the KmerDHT is built for the estimated number of k-mers, then analyze_kmers runs
     dist_object<KmerDHT<MAX_K>> kmer_dht((uint64_t)std::max<uint64_t>(inst, 1000), (int)0, (int)100, false, false);
+    const auto t0 = std::chrono::steady_clock::now();
     analyze_kmers<MAX_K>((unsigned)k, 0u, qual_offset, packed_reads_list, dmin_thres, ctgs, kmer_dht, false);
+    res->t_analyze = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (want_rows) {
     struct Row { std::array<uint64_t, 4> w; uint16_t c; char l, r; };
     std::vector<Row> rows;
     rows.reserve(kmer_dht->get_local_num_kmers());
@@ -176,6 +128,8 @@ int run(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, const uint
       for (int l = 0; l < res->n_longs; l++) res->keys.push_back(row.w[l]);
       res->counts.push_back(row.c); res->left.push_back(row.l); res->right.push_back(row.r);
     }
+    }
+    res->n_local = kmer_dht->get_local_num_kmers();
   }
   return 0;
 }
@@ -195,6 +149,20 @@ void *odrop_run(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, co
   }
   if (rc != 0) { delete res; return nullptr; }
   return res;
+}
+// timing of the seam at bench size: analyze_kmers only, the table stays in local_kmers (no sorted copy); returns seconds
+double odrop_time(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, const uint64_t *offs, uint64_t n_reads,
+                  uint64_t *n_local_kmers) {
+  Result res;
+  int rc = -1;
+  switch ((k / 32 + 1) * 32) {
+    case 32: rc = run<32>(k, qual_offset, dmin_thres, bytes, offs, n_reads, nullptr, nullptr, nullptr, 0, &res, false); break;
+    case 64: rc = run<64>(k, qual_offset, dmin_thres, bytes, offs, n_reads, nullptr, nullptr, nullptr, 0, &res, false); break;
+    case 96: rc = run<96>(k, qual_offset, dmin_thres, bytes, offs, n_reads, nullptr, nullptr, nullptr, 0, &res, false); break;
+    case 128: rc = run<128>(k, qual_offset, dmin_thres, bytes, offs, n_reads, nullptr, nullptr, nullptr, 0, &res, false); break;
+  }
+  if (n_local_kmers) *n_local_kmers = res.n_local;
+  return rc == 0 ? res.t_analyze : -1.0;
 }
 int odrop_n_longs(void *h) { return ((Result *)h)->n_longs; }
 uint64_t odrop_num_survivors(void *h) { return ((Result *)h)->counts.size(); }

@@ -245,10 +245,187 @@ def run_multirank(k, read_bytes, read_offsets, P, dmin_thres=2, workdir=None, ti
         os.rmdir(d)
 
 
+# ---- streaming P-rank run (full-size parity): persistent rank processes, reads fed in chunks (ref_driver.cpp RankWorker) ----
+
+def _worker_main(argv):
+    """One emulated rank as a long-lived process: JSON commands on stdin, one JSON answer per command on stdout."""
+    import json
+    import sys
+    k, P, me, dmin_thres, num_elems, prefix = int(argv[0]), int(argv[1]), int(argv[2]), int(argv[3]), int(argv[4]), argv[5]
+    lib = C.CDLL(REF_SO)
+    lib.oref_w_open.restype = C.c_void_p
+    lib.oref_w_open.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64]
+    lib.oref_w_insert.restype = C.c_double
+    lib.oref_w_insert.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+    lib.oref_w_finish.restype = C.c_double
+    lib.oref_w_finish.argtypes = [C.c_void_p, C.c_void_p]
+    lib.oref_w_free.argtypes = [C.c_void_p]
+    lib.oref_phase_a.restype = C.c_double
+    lib.oref_phase_a.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_char_p, C.c_void_p]
+    lib.oref_phase_a_ctgs.restype = C.c_double
+    lib.oref_phase_a_ctgs.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_char_p,
+                                      C.c_void_p]
+    rb = np.load(prefix + "_bytes.npy", mmap_mode="r")
+    ro = np.load(prefix + "_offs.npy", mmap_mode="r")
+    have_ctg = os.path.exists(prefix + "_cseqs.npy")
+    if have_ctg:
+        cs, co, cd = (np.load(prefix + "_cseqs.npy", mmap_mode="r"), np.load(prefix + "_coffs.npy", mmap_mode="r"),
+                      np.load(prefix + "_cdepths.npy", mmap_mode="r"))
+    w = lib.oref_w_open(k, dmin_thres, P, me, num_elems)
+    if not w:
+        print(json.dumps({"error": "open"}), flush=True)
+        return
+    print(json.dumps({"ok": 1}), flush=True)
+    inst = np.zeros(1, dtype=np.uint64)
+    for line in sys.stdin:
+        cmd = json.loads(line)
+        op = cmd["op"]
+        if op == "a":  # parse my 1/P of reads [lo, hi) with rank_n() = P; supermers go to <chunk>_<me>_<target>.bin
+            lo, hi = cmd["lo"], cmd["hi"]
+            n = hi - lo
+            r0, r1 = lo + n * me // P, lo + n * (me + 1) // P
+            t = lib.oref_phase_a(k, 33, P, me, rb.ctypes.data, ro.ctypes.data, r0, r1, cmd["chunk"].encode(), _p(inst))
+            print(json.dumps({"t": t, "inst": int(inst[0])}), flush=True)
+        elif op == "actg":
+            n = len(co) - 1
+            c0, c1 = n * me // P, n * (me + 1) // P
+            t = lib.oref_phase_a_ctgs(k, P, me, cs.ctypes.data, co.ctypes.data, cd.ctypes.data, c0, c1, cmd["chunk"].encode(), _p(inst))
+            print(json.dumps({"t": t, "inst": int(inst[0])}), flush=True)
+        elif op == "b":
+            t = lib.oref_w_insert(w, cmd["chunk"].encode(), int(cmd.get("ctg", 0)))
+            print(json.dumps({"t": t}), flush=True)
+        elif op == "finish":
+            out = np.zeros(8, dtype=np.uint64)
+            t = lib.oref_w_finish(w, _p(out))
+            print(json.dumps({"t": t, "out": [int(x) for x in out]}), flush=True)
+            lib.oref_w_free(w)
+            return
+
+
+def run_multirank_stream(k, read_bytes, read_offsets, P, dmin_thres=2, ctg_seqs=None, ctg_offsets=None, ctg_depths=None,
+                         chunk_reads=2_000_000, distinct_frac=0.5, workdir=None):
+    """The reference kcount with P emulated ranks (one process each) over the WHOLE read set, reads streamed in chunks so
+    that /dev/shm never holds more than one chunk's supermers. Returns per-rank digests of local_kmers
+    (n, sum counts, sum mix, xor mix) — rank r owns quick_hash(minimizer) % P == r (kmer_dht.cpp:192-196) — plus the
+    bulk-synchronous time (sum over chunks of max parse + max insert) and the reference's dropped / override counters.
+    distinct_frac sizes every rank's table: num_elems = distinct_frac * instances / P (capacity is 3x that)."""
+    import glob
+    import json
+    import sys
+    import tempfile
+    if not have_ref():
+        raise FileNotFoundError(REF_SO)
+    base = workdir or ("/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir())
+    d = tempfile.mkdtemp(prefix="kcrefs_", dir=base)
+    prefix = os.path.join(d, "x")
+    procs = []
+    try:
+        ro = np.ascontiguousarray(read_offsets, dtype=np.uint64)
+        np.save(prefix + "_bytes.npy", np.ascontiguousarray(read_bytes, dtype=np.uint8))
+        np.save(prefix + "_offs.npy", ro)
+        n_reads = len(ro) - 1
+        inst = int(np.maximum(np.diff(ro.astype(np.int64)) - k - 1, 0).sum())
+        have_ctg = ctg_offsets is not None and len(ctg_offsets) > 1
+        if have_ctg:
+            co = np.ascontiguousarray(ctg_offsets, dtype=np.uint64)
+            np.save(prefix + "_cseqs.npy", np.ascontiguousarray(ctg_seqs, dtype=np.uint8))
+            np.save(prefix + "_coffs.npy", co)
+            np.save(prefix + "_cdepths.npy", np.ascontiguousarray(ctg_depths, dtype=np.float64))
+            inst += int(np.maximum(np.diff(co.astype(np.int64)) - k - 1, 0).sum())
+        num_elems = max(1000, int(inst * distinct_frac / P))
+        for me in range(P):
+            procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "worker", str(k), str(P), str(me), str(dmin_thres),
+                                           str(num_elems), prefix], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True, bufsize=1))
+
+        def ask(cmd):
+            line = json.dumps(cmd) + "\n"
+            for pr in procs:
+                pr.stdin.write(line)
+                pr.stdin.flush()
+            out = []
+            for pr in procs:
+                ans = pr.stdout.readline()
+                if not ans:
+                    raise RuntimeError("a reference rank worker died")
+                out.append(json.loads(ans))
+            return out
+
+        for pr in procs:
+            if "ok" not in json.loads(pr.stdout.readline() or '{"error": "died"}'):
+                raise RuntimeError("reference rank worker failed to open its table")
+        t_parse = t_ins = 0.0
+        n_inst = 0
+        ci = 0
+        for lo in range(0, n_reads, chunk_reads):
+            hi = min(n_reads, lo + chunk_reads)
+            chunk = f"{prefix}_c{ci}"
+            ci += 1
+            ra = ask({"op": "a", "lo": lo, "hi": hi, "chunk": chunk})
+            rb_ = ask({"op": "b", "chunk": chunk})
+            t_parse += max(r["t"] for r in ra)
+            t_ins += max(r["t"] for r in rb_)
+            n_inst += sum(r["inst"] for r in ra)
+        if have_ctg:
+            chunk = f"{prefix}_ctg"
+            ra = ask({"op": "actg", "chunk": chunk})
+            rb_ = ask({"op": "b", "chunk": chunk, "ctg": 1})
+            t_parse += max(r["t"] for r in ra)
+            t_ins += max(r["t"] for r in rb_)
+            n_inst += sum(r["inst"] for r in ra)
+        rf = ask({"op": "finish"})
+        t_ins += max(r["t"] for r in rf)
+        outs = [r["out"] for r in rf]
+        for pr in procs:
+            pr.stdin.close()
+            pr.wait(timeout=60)
+        return dict(seconds=t_parse + t_ins, seconds_parse=t_parse, seconds_insert=t_ins, instances=n_inst, ranks=P,
+                    digests=[tuple(o[:4]) for o in outs], survivors=sum(o[0] for o in outs), distinct=sum(o[4] for o in outs),
+                    dropped=sum(o[5] for o in outs), singleton_overrides=sum(o[6] for o in outs))
+    finally:
+        for pr in procs:
+            if pr.poll() is None:
+                pr.kill()
+        for f in glob.glob(os.path.join(d, "*")):
+            os.remove(f)
+        os.rmdir(d)
+
+
+def combine_digests(digests, n_groups=1):
+    """Per-rank digests of a P-rank run -> digests of n_groups shards, shard g = ranks r with r % n_groups == g (valid because
+    n_groups divides P: x % P % n_groups == x % n_groups)."""
+    M = (1 << 64) - 1
+    out = []
+    for g in range(n_groups):
+        n = sc = sm = xm = 0
+        for r in range(g, len(digests), n_groups):
+            a, b, c, e = digests[r]
+            n += a
+            sc += b
+            sm = (sm + c) & M
+            xm ^= e
+        out.append((n, sc, sm, xm))
+    return out
+
+
+def pack_reads_ref(seqs, quals, offsets, qual_offset=33):
+    """FASTQ text -> PackedRead bytes through the reference's own PackedRead constructor (packed_reads.cpp:73-109)."""
+    lib = C.CDLL(REF_SO)
+    lib.oref_pack_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    s = np.ascontiguousarray(seqs, dtype=np.uint8)
+    q = np.ascontiguousarray(quals, dtype=np.uint8)
+    o = np.ascontiguousarray(offsets, dtype=np.uint64)
+    out = np.empty(int(o[-1]), dtype=np.uint8)
+    if lib.oref_pack_reads(_p(s), _p(q), _p(o), len(o) - 1, qual_offset, _p(out)) != 0:
+        raise RuntimeError("oref_pack_reads failed")
+    return out
+
+
 if __name__ == "__main__":
     import sys
     if len(sys.argv) > 1 and sys.argv[1] == "phase":
         _phase_main(sys.argv[2:])
+    elif len(sys.argv) > 1 and sys.argv[1] == "worker":
+        _worker_main(sys.argv[2:])
 
 
 # ---- drop-in proof: the reference's own analyze_kmers with integration/kcount_b200.cpp as its backend (dropin_driver.cpp) ----

@@ -396,3 +396,177 @@ double oref_phase_b(int k, int dmin_thres, int P, int me, const char *prefix, ui
   return -1;
 }
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// (f-2) checker: FASTQ text -> PackedRead bytes through the reference's OWN constructor (packed_reads.cpp:73-109, compiled
+// unmodified into _ref/packed_reads.o)
+#include "packed_reads.hpp"
+extern "C" int oref_pack_reads(const char *seqs, const char *quals, const uint64_t *offs, uint64_t n, int qual_offset, uint8_t *out) {
+  for (uint64_t r = 0; r < n; r++) {
+    const size_t len = offs[r + 1] - offs[r];
+    std::string id = "@r" + std::to_string(r / 2) + "/" + ((r & 1) ? "2" : "1");
+    PackedRead pr(id, std::string_view(seqs + offs[r], len), std::string_view(quals + offs[r], len), qual_offset);
+    if (pr.get_read_len() != (uint16_t)len) return -1;
+    memcpy(out + offs[r], pr.get_raw_bytes(), len);
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Streaming P-rank emulation: the same two phases as above, but the reads arrive in chunks and every emulated rank keeps
+// ITS table (the reference's KmerDHT + HashTableInserter) alive between chunks, so a full-size workload (C2: 3.25 G
+// instances) never needs more than one chunk's supermers in /dev/shm. finish() returns the order-independent digest of the
+// rank's local_kmers — the same function kc_table_digest computes on the device (include/kcount_b200.h) — for the
+// full-size parity check of bench.py, plus the reference's own dropped / singleton-override counters, which must be zero.
+namespace {
+inline uint64_t dg_fmix64(uint64_t k) {  // MurmurHash3's finaliser (hash_funcs.c:65-74)
+  k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33;
+  return k;
+}
+
+struct RankWorker {
+  virtual ~RankWorker() {}
+  virtual double insert(const char *prefix, int is_ctg) = 0;
+  virtual double finish(uint64_t *out8) = 0;
+};
+
+template <int MAX_K>
+struct RankWorkerImpl : RankWorker {
+  int k, P, me;
+  dist_object<KmerDHT<MAX_K>> dht;
+  bool ctg_mode = false;
+  uint64_t dropped = 0;
+  RankWorkerImpl(int k, int dmin_thres, int P, int me, uint64_t num_elems)
+      : k(k), P(P), me(me), dht((uint64_t)num_elems, (int)0, (int)100, false, false) {
+    _dmin_thres = dmin_thres;
+  }
+  double insert(const char *prefix, int is_ctg) override {
+    using clk = std::chrono::steady_clock;
+    auto t0 = clk::now();
+    if (is_ctg && !ctg_mode) {  // kcount.cpp:148-150: the reads pass is flushed before the contig pass starts
+      dropped += dht->ht_inserter->state->kmers->get_num_dropped();
+      dht->flush_updates();
+      dht->ht_inserter->init_ctg_kmers(0);
+      ctg_mode = true;
+    }
+    std::string buf, seq;
+    for (int src = 0; src < P; src++) {
+      std::string fn = std::string(prefix) + "_" + std::to_string(src) + "_" + std::to_string(me) + ".bin";
+      FILE *f = fopen(fn.c_str(), "rb");
+      if (!f) continue;
+      fseek(f, 0, SEEK_END);
+      long sz = ftell(f);
+      fseek(f, 0, SEEK_SET);
+      buf.resize(sz);
+      const bool ok = !sz || fread(&buf[0], 1, sz, f) == (size_t)sz;
+      fclose(f);
+      remove(fn.c_str());
+      if (!ok) return -1;
+      size_t pos = 0;
+      while (pos + 6 <= (size_t)sz) {
+        uint16_t cnt; uint32_t len;
+        memcpy(&cnt, &buf[pos], 2); memcpy(&len, &buf[pos + 2], 4);
+        pos += 6;
+        seq.assign(&buf[pos], len);
+        pos += len;
+        dht->ht_inserter->insert_supermer(seq, cnt);  // what the store's update_func does (kmer_dht.cpp:146-149)
+      }
+    }
+    return std::chrono::duration<double>(clk::now() - t0).count();
+  }
+  double finish(uint64_t *out8) override {
+    using clk = std::chrono::steady_clock;
+    auto t0 = clk::now();
+    auto &tab = *dht->ht_inserter->state->kmers;
+    const uint64_t distinct = tab.size();
+    dropped += tab.get_num_dropped();
+    const uint64_t overrides = tab.get_num_singleton_overrides();
+    dht->flush_updates();
+    dht->finish_updates();
+    auto t1 = clk::now();
+    const int nl = (int)Kmer<MAX_K>::get_N_LONGS();
+    uint64_t n = 0, sc = 0, sm = 0, xm = 0;
+    for (auto it = dht->local_kmers_begin(); it != dht->local_kmers_end(); ++it) {
+      uint64_t x = 0x9E3779B97F4A7C15ULL;
+      for (int l = 0; l < nl; l++) x = dg_fmix64(x ^ it->first.get_longs()[l]);
+      const uint64_t c = it->second.count;
+      x = dg_fmix64(x ^ (c | ((uint64_t)(unsigned char)it->second.left << 16) | ((uint64_t)(unsigned char)it->second.right << 24)));
+      n++; sc += c; sm += x; xm ^= x;
+    }
+    out8[0] = n; out8[1] = sc; out8[2] = sm; out8[3] = xm; out8[4] = distinct; out8[5] = dropped; out8[6] = overrides; out8[7] = 0;
+    return std::chrono::duration<double>(t1 - t0).count();
+  }
+};
+
+// phase A for contigs: process_seq(ctg.seq, ctg.get_uint16_t_depth()) (kcount.cpp:123-130) with rank_n() = P
+template <int MAX_K>
+double phase_a_ctgs(int k, int P, int me, const char *cseqs, const uint64_t *coffs, const double *cdepths, uint64_t c0, uint64_t c1,
+                    const char *prefix, uint64_t *out_inst) {
+  using clk = std::chrono::steady_clock;
+  Kmer<MAX_K>::set_k(k);
+  upcxx::shim_state::nranks() = P;
+  upcxx::shim_state::me() = me;
+  upcxx_utils::shim_mem::free_mem() = 1e9;
+  std::vector<std::string> bufs(P);
+  upcxx_utils::ThreeTierAggrStore<Supermer>::tap() = [&bufs](int target, const Supermer &s) {
+    std::string &b = bufs[target];
+    uint32_t len = (uint32_t)s.seq.size();
+    uint16_t cnt = s.count;
+    b.append((const char *)&cnt, 2);
+    b.append((const char *)&len, 4);
+    b.append(s.seq);
+    return true;
+  };
+  dist_object<KmerDHT<MAX_K>> kmer_dht((uint64_t)1000, (int)0, (int)100, false, false);
+  auto t0 = clk::now();
+  SeqBlockInserter<MAX_K> sbi(0, kmer_dht->get_minimizer_len());
+  std::string seq;
+  uint64_t inst = 0;
+  for (uint64_t c = c0; c < c1; c++) {
+    size_t len = coffs[c + 1] - coffs[c];
+    if (len < (size_t)k + 2) continue;  // kcount.cpp:126
+    seq.assign(cseqs + coffs[c], len);
+    Contig ctg{.id = (int64_t)c, .seq = "", .depth = cdepths[c]};
+    sbi.process_seq(seq, ctg.get_uint16_t_depth(), kmer_dht);
+    inst += len - k - 1;
+  }
+  for (int t = 0; t < P; t++) {
+    std::string fn = std::string(prefix) + "_" + std::to_string(me) + "_" + std::to_string(t) + ".bin";
+    FILE *f = fopen(fn.c_str(), "wb");
+    if (f) { fwrite(bufs[t].data(), 1, bufs[t].size(), f); fclose(f); }
+  }
+  auto t1 = clk::now();
+  upcxx_utils::ThreeTierAggrStore<Supermer>::tap() = nullptr;
+  *out_inst = inst;
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+}  // namespace
+
+extern "C" {
+void *oref_w_open(int k, int dmin_thres, int P, int me, uint64_t num_elems) {
+  upcxx::shim_state::nranks() = P;
+  upcxx::shim_state::me() = me;
+  upcxx_utils::shim_mem::free_mem() = 3.2 * (double)num_elems * (8 * (k / 32 + 1) + 20) / 0.6;
+  if (num_elems > 700000000ull) return nullptr;
+  switch ((k / 32 + 1) * 32) {
+    case 32: Kmer<32>::set_k(k); return new RankWorkerImpl<32>(k, dmin_thres, P, me, num_elems);
+    case 64: Kmer<64>::set_k(k); return new RankWorkerImpl<64>(k, dmin_thres, P, me, num_elems);
+    case 96: Kmer<96>::set_k(k); return new RankWorkerImpl<96>(k, dmin_thres, P, me, num_elems);
+    case 128: Kmer<128>::set_k(k); return new RankWorkerImpl<128>(k, dmin_thres, P, me, num_elems);
+  }
+  return nullptr;
+}
+double oref_w_insert(void *w, const char *prefix, int is_ctg) { return ((RankWorker *)w)->insert(prefix, is_ctg); }
+double oref_w_finish(void *w, uint64_t *out8) { return ((RankWorker *)w)->finish(out8); }
+void oref_w_free(void *w) { delete (RankWorker *)w; }
+double oref_phase_a_ctgs(int k, int P, int me, const char *cseqs, const uint64_t *coffs, const double *cdepths, uint64_t c0, uint64_t c1,
+                         const char *prefix, uint64_t *out_inst) {
+  switch ((k / 32 + 1) * 32) {
+    case 32: return phase_a_ctgs<32>(k, P, me, cseqs, coffs, cdepths, c0, c1, prefix, out_inst);
+    case 64: return phase_a_ctgs<64>(k, P, me, cseqs, coffs, cdepths, c0, c1, prefix, out_inst);
+    case 96: return phase_a_ctgs<96>(k, P, me, cseqs, coffs, cdepths, c0, c1, prefix, out_inst);
+    case 128: return phase_a_ctgs<128>(k, P, me, cseqs, coffs, cdepths, c0, c1, prefix, out_inst);
+  }
+  return -1;
+}
+}

@@ -9,6 +9,7 @@
 #include <memory>
 #include <utility>
 #include <type_traits>
+#include <tuple>
 
 #define UPCXX_SERIALIZED_FIELDS(...)
 
@@ -62,6 +63,20 @@ struct future<T> {
 inline future<> make_future() { return future<>(); }
 template <typename T>
 future<T> make_future(T v) { return future<T>{v}; }
+
+// fastq.hpp (pulled in by packed_reads.cpp) declares members of these types; nothing on the kcount path calls them
+template <typename... T>
+struct promise {
+  std::tuple<T...> v;
+  template <typename... A>
+  void fulfill_result(A &&...a) { v = std::tuple<T...>(std::forward<A>(a)...); }
+  future<T...> get_future() const {
+    if constexpr (sizeof...(T) == 0) return future<>();
+    else return future<T...>{std::get<0>(v)};
+  }
+};
+template <typename... F>
+future<> when_all(F &&...) { return future<>(); }
 
 struct op_add_t {}; struct op_max_t {}; struct op_min_t {};
 static constexpr op_add_t op_fast_add{};

@@ -64,5 +64,27 @@ def main():
             print(k, tag, len(res.counts), "survivors", len(res.pf_vals), "distinct")
 
 
+def packed_reads_golden():
+    """FASTQ text -> PackedRead bytes through the reference's own constructor (packed_reads.cpp:73-109, compiled unmodified
+    into oracle/_ref): pins kc_reads_create_fastq. Includes IUPAC codes, qualities above the 31 clamp and
+    below the offset (the unsigned-char wrap), ragged lengths."""
+    com = synth.make_community(20000, n_genomes=1, seed=77)
+    rb, ro = synth.make_reads(400, com, error_rate=0.01, seed=78, n_rate=5e-3, var_len=True)
+    rng = np.random.default_rng(79)
+    iupac = np.frombuffer(b"NURYKMSWBDHV", dtype=np.uint8)
+    seq = np.frombuffer(b"ACGTN", dtype=np.uint8)[rb & 7].copy()
+    isn = (rb & 7) == 4
+    seq[isn] = iupac[rng.integers(0, len(iupac), int(isn.sum()))]
+    qual = (rb >> 3).astype(np.int64) + 33
+    odd = rng.random(len(rb)) < 0.02
+    qual[odd] = rng.integers(33 - 3, 33 + 60, int(odd.sum()))
+    qual = qual.astype(np.uint8)
+    packed = H.pack_reads_ref(seq, qual, ro, 33)
+    np.savez_compressed(os.path.join(HERE, "packed_reads.npz"), seqs=seq, quals=qual, offsets=ro, packed=packed, qual_offset=33)
+    print("packed_reads", len(ro) - 1, "reads", len(packed), "bytes")
+
+
 if __name__ == "__main__":
-    main()
+    if "--packed-only" not in sys.argv:
+        main()
+    packed_reads_golden()

@@ -29,8 +29,10 @@ def test_struct_layouts_match_header(built):
     # defaults are the reference's constants (CMakeDefinitions.txt:46,60; options.hpp:96)
     assert (cfg.kmer_len, cfg.qual_cutoff, cfg.dmin_thres, cfg.num_shards) == (31, 20, 2, 1)
     assert abs(cfg.dyn_min_depth - 0.9) < 1e-15
-    assert ctypes.sizeof(kcount.KcConfig) == 80
-    assert ctypes.sizeof(kcount.KcStats) == 16 * 8 + 10 * 8 + 5 * 8 + 4 * 8
+    a, b = ctypes.c_uint32(), ctypes.c_uint32()
+    lib.kc_struct_sizes(ctypes.byref(a), ctypes.byref(b))
+    assert ctypes.sizeof(kcount.KcConfig) == a.value == 80
+    assert ctypes.sizeof(kcount.KcStats) == b.value == (17 + 9 + 4 + 4) * 8
 
 
 def test_no_gpu_means_loud_failure(built):

