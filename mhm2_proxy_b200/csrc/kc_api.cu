@@ -1023,25 +1023,32 @@ extern "C" int kc_set_dmin_thres(kc_handle *h, int32_t dmin_thres) {
 
 namespace {
 
-template <int KW, bool WIDE, bool CTG>
+template <int KW, bool WIDE, bool CTG, int KC>
 int launch_count(kc_handle *h, const CountArgs &ca, size_t smem, unsigned grid) {
-  CK(cudaFuncSetAttribute(count_kernel<KW, WIDE, CTG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  count_kernel<KW, WIDE, CTG><<<grid, CNT_THREADS, smem, h->s_main>>>(ca);
+  CK(cudaFuncSetAttribute(count_kernel<KW, WIDE, CTG, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  count_kernel<KW, WIDE, CTG, KC><<<grid, CNT_THREADS, smem, h->s_main>>>(ca);
   CK(cudaGetLastError());
   return KC_OK;
 }
 
+// The reference's default k schedule (options.cpp:373: 21,33,55,77,99) and k=31 get kernels with k folded in at compile time
+// (narrow counters; kc_extract.cuh); every other k, and the rare wide re-runs, take the run-time-k kernels.
 int dispatch_count(kc_handle *h, bool wide, bool ctg, const CountArgs &ca, size_t smem, unsigned grid) {
+  static const bool fixed_ok = !(getenv("KC_FIXED_K") && atoi(getenv("KC_FIXED_K")) == 0);  // A/B switch
+#define GOK(KWv, Kv)                                                                                   \
+  if (fixed_ok && !wide && h->cfg.kmer_len == Kv)                                                      \
+    return ctg ? launch_count<KWv, false, true, Kv>(h, ca, smem, grid) : launch_count<KWv, false, false, Kv>(h, ca, smem, grid)
 #define GO3(KWv)                                                                               \
-  return wide ? (ctg ? launch_count<KWv, true, true>(h, ca, smem, grid) : launch_count<KWv, true, false>(h, ca, smem, grid)) \
-              : (ctg ? launch_count<KWv, false, true>(h, ca, smem, grid) : launch_count<KWv, false, false>(h, ca, smem, grid))
+  return wide ? (ctg ? launch_count<KWv, true, true, 0>(h, ca, smem, grid) : launch_count<KWv, true, false, 0>(h, ca, smem, grid)) \
+              : (ctg ? launch_count<KWv, false, true, 0>(h, ca, smem, grid) : launch_count<KWv, false, false, 0>(h, ca, smem, grid))
   switch (h->KW) {
-    case 1: GO3(1);
-    case 2: GO3(2);
-    case 3: GO3(3);
-    case 4: GO3(4);
+    case 1: GOK(1, 21); GOK(1, 31); GO3(1);
+    case 2: GOK(2, 33); GOK(2, 55); GO3(2);
+    case 3: GOK(3, 77); GO3(3);
+    case 4: GOK(4, 99); GO3(4);
   }
 #undef GO3
+#undef GOK
   return fail(h, KC_ERR_INVALID, "unsupported key width %d", h->KW);
 }
 

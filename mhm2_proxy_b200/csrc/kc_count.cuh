@@ -26,6 +26,7 @@
 #pragma once
 #include "kc_device.cuh"
 #include "kc_parse.cuh"
+#include "kc_extract.cuh"
 
 namespace kc {
 
@@ -56,7 +57,7 @@ struct WorkItem {
   u32 part;
   u32 sub, nsub;           // this item takes k-mers with ((hash >> 40) & (nsub - 1)) == sub; nsub is a power of two
   u32 heavy;               // far above the mean: scheduled through CountArgs::heavy ahead of everything else
-  u32 pad;
+  u32 ninst;               // k-mer instances of the partition (saturating): < 65536 means no u16 counter can wrap
 };
 
 struct BlockDesc {  // one parsed or received batch as the item builder sees it (all pointers are device memory)
@@ -121,15 +122,31 @@ __device__ __forceinline__ uint4 lds128_volatile(u32 a) {  // a: shared-space ad
   return v;
 }
 
+__device__ __forceinline__ u64 lds64_volatile(u32 a) {
+  u64 v;
+  asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void atoms_add(u32 a, u32 v) {  // shared-space address; no result wanted (RED-style)
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ u32 atoms_add_ret(u32 a, u32 v) {
+  u32 old;
+  asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(a), "r"(v) : "memory");
+  return old;
+}
+
 // 0..5 -> A C G T F X
 __device__ __forceinline__ char ext_char(u32 c) { return c < 4u ? (char)((0x54474341u >> (8u * c)) & 0xFFu) : (c == 4u ? 'F' : 'X'); }
 
-template <int KW, bool WIDE, bool CTG>
+// KC: k as a compile-time constant (0 = any k at run time, taken from CountArgs), see kc_extract.cuh
+template <int KW, bool WIDE, bool CTG, int KC>
 __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a) {
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int sw = stage_words(a.rw);
+  const int k = KC ? KC : a.k, rw = KC ? kc_rw_of(KC ? KC : 21) : a.rw;
+  const int sw = stage_words(rw);
   u32 *stage_all = (u32 *)smem_raw;                        // [CNT_GROUPS][sw], 16-byte aligned rows (sw % 4 == 0)
   u32 *tab = stage_all + CNT_GROUPS * sw;                  // [tab_size], 16-byte buckets
   u64 *keys = (u64 *)(tab + a.tab_size);                   // [key_cap * KW]
@@ -145,16 +162,15 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const int grp = wid, gt = lane;  // pipeline = warp
   u32 *stage = stage_all + grp * sw;
   uint16_t *expl = expl_all[grp];
-  const int k = a.k, rw = a.rw;
-  const int nw = KW == 1 ? 1 : (k + 31) >> 5;  // words of the key that hold bases: KW, or KW - 1 when k % 32 == 0
-  const u64 last_mask = (k & 31) ? (~0ULL << (64 - 2 * (k & 31))) : ~0ULL;
-  const int rsh = 62 - 2 * (k & 31);  // where the base after the k-mer sits in the k-mer's last word (k % 32 != 0)
   const u32 nbuckets = a.tab_size >> 2;
-  const u32 tab_s = (u32)__cvta_generic_to_shared(tab);
-  const int nwb = a.nwb;
+  const u32 tab_s = (u32)__cvta_generic_to_shared(tab), keys_s = (u32)__cvta_generic_to_shared(keys),
+            vals_s = (u32)__cvta_generic_to_shared(vals), stage_s = (u32)__cvta_generic_to_shared(stage),
+            expl_s = (u32)__cvta_generic_to_shared(expl);
+  const int nwb = KC ? kc_nwb_of(KC ? KC : 21) : a.nwb;
+  const int w_ = KC ? kc_w_of(KC ? KC : 21) : a.w;
   // supermers staged per chunk: what the staging buffer holds, and no more than the instance list will take (a supermer has
   // (w + 1) / 2 k-mers on average; staging records that do not fit the list means staging them again)
-  const int sup_per_chunk = min(min(GRP_THREADS, GRP_STAGE_MAX / rw), 2 * GRP_EXP / (a.w + 1) + 3);
+  const int sup_per_chunk = min(min(GRP_THREADS, GRP_STAGE_MAX / rw), 2 * GRP_EXP / (w_ + 1) + 3);
   u32 my_max_probe = 0;
   // Work items are dealt round-robin to the CTAs: first the heavy list (outlier partitions, heaviest first, so that none of
   // them starts last and becomes the tail), then every item in partition order, skipping the ones the heavy list covered.
@@ -204,6 +220,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
     for (u32 i = tid; i < prev * VW; i += CNT_THREADS) vals[i] = 0;  // counters of the slots the previous item used
     __syncthreads();
     const u32 nseg = it.seg_end - it.seg_begin;
+    const bool may_wrap = it.ninst >= 65536u;
     u32 spare = 0xFFFFFFFFu;  // a dense entry this thread reserved but could not publish (same key claimed concurrently)
 
     for (u32 sg0 = 0; sg0 < nseg; sg0 += SEG_CACHE) {
@@ -254,95 +271,76 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         __syncwarp();
 
         // ---- c. every k-mer instance of the chunk ----
-        for (u32 t = gt; t < total; t += GRP_THREADS) {
-          const u32 e = expl[t];
-          const u32 si = e & 255u;
-          const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
-          const u32 *rec = stage + si * rw;
-          const u32 hdr = CTG ? rec[0] : 0u;
-          const u32 *p = rec + 1;
-          const u32 *pv = p + nwb;
-          // words idx-1 .. idx+2*nw of the base stream hold the base before the k-mer, the k-mer and (k % 32 != 0) the base
-          // after it: one pass of funnel shifts yields all three (p[-1] is the header word, read but never selected)
-          const u32 *pw = p + (j >> 4);
-          const u32 sh = (u32)(j & 15) * 2u;
-          u32 wv[2 * KW + 2];
+        // Fast path (about 7 of 8 instances at 33x coverage): extract, hash, ONE 128-bit bucket load, key compare, two counter
+        // adds. A miss (new key, shared fingerprint, full bucket) needs the probe-and-claim path, ~70 instructions that ran
+        // with 4 of 32 lanes active when every lane handled its own miss at once. Misses are therefore DEFERRED: the lane
+        // parks (key, slots) in registers and goes on; the warp runs the slow path only when a lane with a parked miss misses
+        // again or DEFER_AT lanes are waiting, i.e. every third or fourth iteration with a dozen lanes active. Counter
+        // updates commute, so the order of inserts is free. (KW >= 3: a parked key would cost 6-8 registers; not deferred.)
+        constexpr bool DEFER = KW <= 2;
+        constexpr u32 DEFER_AT = 20;
+        bool pend = false;
+        u64 pkey[KW];
+        u32 pmeta = 0;
 #pragma unroll
-          for (int i = 0; i < 2 * KW + 2; i++) wv[i] = (i <= 2 * nw + 1) ? pw[i - 1] : 0u;
-          u64 fwd[KW], rc[KW];
-#pragma unroll
-          for (int i = 0; i < KW; i++)
-            fwd[i] = ((u64)__funnelshift_l(wv[2 * i + 2], wv[2 * i + 1], sh) << 32) | __funnelshift_l(wv[2 * i + 3], wv[2 * i + 2], sh);
-          const int lcode = (int)(__funnelshift_l(wv[1], wv[0], sh) & 3u);
-          // word nw - 1 keeps only its k % 32 bases; nw is KW or KW - 1 (static indices: no local memory). Before the mask
-          // the same word still holds the base that follows the k-mer.
-          const u64 lastw = (nw == KW) ? fwd[KW - 1] : fwd[KW >= 2 ? KW - 2 : 0];
-          const int rcode = (k & 31) ? (int)((u32)(lastw >> rsh) & 3u) : fetch_base(p, j + k);
-          if (nw == KW) fwd[KW - 1] &= last_mask;
-          else if (KW >= 2) { fwd[KW >= 2 ? KW - 2 : 0] &= last_mask; fwd[KW - 1] = 0ULL; }
-          int lval, rval;
-          if (k <= 30) {  // both extension-valid bits sit in one 32-bit window of the bit stream
-            const int q = j - 1;
-            const u32 vw = __funnelshift_r(pv[q >> 5], pv[(q >> 5) + 1], (u32)q & 31u);
-            lval = (int)(vw & 1u);
-            rval = (int)((vw >> (k + 1)) & 1u);
-          } else {
-            lval = fetch_bit(pv, j - 1);
-            rval = fetch_bit(pv, j + k);
+        for (int i = 0; i < KW; i++) pkey[i] = 0;
+        // counters of dense entry idx: meta = left slot | right slot << 3 | (contigs) header bits 15..31
+        auto update = [&](u32 idx, u32 meta) {
+          const u32 sl = meta & 7u, sr = (meta >> 3) & 7u;
+          const u32 va = vals_s + idx * (u32)(VW * 4);
+          if (!CTG || !(meta & 0x8000u)) {  // a read instance (count 1: kcount_cpu.cpp:75,348-352)
+            if (WIDE) {
+              atoms_add(va + 4u * sl, 1u);
+              if (sr < 4u) atoms_add(va + 4u * (5u + sr), 1u);
+            } else {
+              // u16 halves: left slots 0..4 are halves 0..4, right slots 0..4 halves 5..9 (half 9 = right "none": a spare that
+              // is never read, so the right add needs no predicate). A half that was 0xFFFF before the add has wrapped (into
+              // its neighbour): the item is re-run with wide counters. Items of < 65536 instances cannot wrap: no check.
+              const u32 hl = sl, hr = 5u + sr;
+              const u32 il = 1u + (hl & 1u) * 0xFFFFu, ir = 1u + (hr & 1u) * 0xFFFFu;
+              if (may_wrap) {
+                u32 old = atoms_add_ret(va + ((hl << 1) & ~3u), il);
+                if ((old | ((hl & 1u) ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
+                if (sr < 4u) {
+                  old = atoms_add_ret(va + ((hr << 1) & ~3u), ir);
+                  if ((old | ((hr & 1u) ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
+                }
+              } else {
+                atoms_add(va + ((hl << 1) & ~3u), il);
+                atoms_add(va + ((hr << 1) & ~3u), ir);
+              }
+            }
+          } else {  // a contig instance: remembered as (occurrences, min depth, set of extension pairs), DESIGN.md "contig pass"
+            u32 *v = vals + (size_t)idx * VW;
+            atomicAdd(v + VR, 1u);
+            atomicMax(v + VR + 1, ~(meta >> 16));
+            atomicOr(v + VR + 2, 1u << (sl * 5 + sr));
           }
-          revcomp_words<KW>(fwd, rc, k);
-          int l, r;
-          u64 key[KW];
-          const bool use_rc = words_less<KW>(rc, fwd);  // strict: palindromes keep the forward orientation (kcount_cpu.cpp:326-331)
-#pragma unroll
-          for (int i = 0; i < KW; i++) key[i] = use_rc ? rc[i] : fwd[i];
-          if (use_rc) {  // swap + complement the extensions (kcount_cpu.cpp:328-330)
-            l = rval ? 3 - rcode : EXT_NONE;
-            r = lval ? 3 - lcode : EXT_NONE;
-          } else {
-            l = lval ? lcode : EXT_NONE;
-            r = rval ? rcode : EXT_NONE;
-          }
-          const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
-          if (it.nsub > 1 && ((u32)(h >> 40) & (it.nsub - 1)) != it.sub) continue;
-          // ---- find or claim: one 128-bit load per bucket, everything else on registers ----
-          const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);  // never 0, so an empty entry never matches
+        };
+        // probe and claim: returns the key's dense entry, or 0xFFFFFFFF when the key store is full (the item is re-run)
+        auto find_or_claim = [&](const u64 (&key)[KW]) -> u32 {
+          const u64 h = table_hash<KW>(key);
+          const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
           u32 bkt = __umulhi((u32)h, nbuckets);
-          u32 mine = 0xFFFFFFFFu, idx = 0xFFFFFFFFu, probes = 0;
+          u32 idx = 0xFFFFFFFFu, mine = 0xFFFFFFFFu, probes = 0;
           bool claimed = false;
           for (;;) {
             const uint4 bq = lds128_volatile(tab_s + 16u * bkt);
-            // an entry matches when its upper 19 bits equal the fingerprint (fp has bit 13 set: an empty entry never does)
-            const bool m0 = (bq.x ^ fp) <= IDX_MASK, m1 = (bq.y ^ fp) <= IDX_MASK, m2 = (bq.z ^ fp) <= IDX_MASK, m3 = (bq.w ^ fp) <= IDX_MASK;
-            if (m0 | m1 | m2 | m3) {  // almost always exactly one candidate, and it is the key
-              const u32 en = m0 ? bq.x : m1 ? bq.y : m2 ? bq.z : bq.w;
-              const u32 cand = (en & IDX_MASK) - 1u;
-              bool same = true;
-#pragma unroll
-              for (int i = 0; i < KW; i++) same = same && (((volatile u64 *)keys)[(size_t)cand * KW + i] == key[i]);
-              if (same) {
-                idx = cand;
-                break;
-              }
-              // rare (2^-18 per occupied entry): another key with our fingerprint came first; check the candidates after it
-              bool first = true;
+            const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
+            if (mn <= IDX_MASK) {  // some entry carries our fingerprint: almost always the key itself (claimed meanwhile)
 #pragma unroll
               for (int q = 0; q < 4; q++) {
                 const u32 eq = q == 0 ? bq.x : q == 1 ? bq.y : q == 2 ? bq.z : bq.w;
                 if ((eq ^ fp) <= IDX_MASK && idx == 0xFFFFFFFFu) {
-                  if (first) {
-                    first = false;
-                  } else {
-                    const u32 c2 = (eq & IDX_MASK) - 1u;
-                    bool s2 = true;
+                  const u32 c2 = (eq & IDX_MASK) - 1u;
+                  bool s2 = true;
 #pragma unroll
-                    for (int i = 0; i < KW; i++) s2 = s2 && (((volatile u64 *)keys)[(size_t)c2 * KW + i] == key[i]);
-                    if (s2) idx = c2;
-                  }
+                  for (int i = 0; i < KW; i++) s2 = s2 && (lds64_volatile(keys_s + c2 * (u32)(KW * 8) + 8u * i) == key[i]);
+                  if (s2) idx = c2;
                 }
               }
+              if (idx != 0xFFFFFFFFu) break;
             }
-            if (idx != 0xFFFFFFFFu) break;
             // entries of a bucket are claimed in order and never removed, so the occupied ones are a prefix: the bucket has
             // room iff its last entry is empty, and the first empty entry is the number of occupied ones (a stale view can
             // only point at an entry that is already taken: the CAS fails and the bucket is read again)
@@ -368,38 +366,79 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
                 claimed = true;
                 break;
               }
-              continue;  // somebody else took that entry: look at this bucket again (it may now hold our key)
+              // somebody else took that entry: look at this bucket again (it may now hold our key)
+            } else {
+              probes++;
+              bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
             }
-            probes++;
-            bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
           }
           if (mine != 0xFFFFFFFFu && !claimed && mine < a.key_cap) {  // lost a same-key race: the entry stays ours for the next new key
             keys[(size_t)mine * KW + KW - 1] = KEY_EMPTY;
             spare = mine;
           }
-          if (idx == 0xFFFFFFFFu) continue;  // out of key slots; the item is re-run
           my_max_probe = max(my_max_probe, probes);
-          u32 *v = vals + (size_t)idx * VW;
-          if (!CTG || !(hdr & 0x8000u)) {  // a read instance (count 1: kcount_cpu.cpp:75,348-352)
-            if (WIDE) {
-              atomicAdd(v + l, 1u);
-              if (r < 4) atomicAdd(v + 5 + r, 1u);
+          return idx;
+        };
+        // one more (empty) iteration after the last instance flushes what is still parked
+        for (u32 t0 = 0; t0 < total + (DEFER ? GRP_THREADS : 0u); t0 += GRP_THREADS) {
+          const u32 t = t0 + (u32)gt;
+          bool miss = false;
+          u64 key[KW];
+          u32 meta = 0;
+          if (t < total) {
+            const u32 e = lds16(expl_s + 2u * t);
+            const u32 si = e & 255u;
+            const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
+            Instance in;
+            u32 hdr = 0u;
+            if (KC) {
+              const u32 rec_s = stage_s + si * (u32)(rw * 4);
+              if (CTG) hdr = lds32(rec_s);
+              in = extract_fixed<KW, KC ? KC : 21>(rec_s, j, key);
             } else {
-              // a half that was 0xFFFF before the add has wrapped (into its neighbour): the item is re-run with wide counters
-              const bool lodd = (l & 1) != 0;
-              u32 old = atomicAdd(v + (l >> 1), lodd ? 0x10000u : 1u);
-              if ((old | (lodd ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
-              if (r < 4) {
-                const u32 hr = 5u + (u32)r;
-                const bool rodd = (hr & 1u) != 0;
-                old = atomicAdd(v + (hr >> 1), rodd ? 0x10000u : 1u);
-                if ((old | (rodd ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
+              const u32 *rec = stage + si * rw;
+              if (CTG) hdr = rec[0];
+              in = extract_any<KW>(rec, j, k, nwb, key);
+            }
+            meta = in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u);
+            const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
+            if (it.nsub <= 1 || ((u32)(h >> 40) & (it.nsub - 1)) == it.sub) {
+              // find: one 128-bit load of the bucket. entry ^ fp is (dense index + 1) <= IDX_MASK exactly when the entry's upper
+              // 19 bits equal the fingerprint (fp has bit 13 set: an empty entry never matches), so the minimum over the four
+              // words IS the candidate's index + 1 — no selects
+              const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
+              const uint4 bq = lds128_volatile(tab_s + 16u * __umulhi((u32)h, nbuckets));
+              const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
+              miss = true;
+              if (mn <= IDX_MASK) {
+                const u32 ka = keys_s + (mn - 1u) * (u32)(KW * 8);
+                bool same = true;
+#pragma unroll
+                for (int i = 0; i < KW; i++) same = same && (lds64_volatile(ka + 8u * i) == key[i]);
+                if (same) {
+                  miss = false;
+                  update(mn - 1u, meta);
+                }
               }
             }
-          } else {  // a contig instance: remembered as (occurrences, min depth, set of extension pairs), DESIGN.md "contig pass"
-            atomicAdd(v + VR, 1u);
-            atomicMax(v + VR + 1, ~(hdr >> 16));
-            atomicOr(v + VR + 2, 1u << (l * 5 + r));
+          }
+          if (DEFER) {
+            const bool flush = __any_sync(0xffffffffu, miss && pend) || t0 >= total ||
+                               (u32)__popc(__ballot_sync(0xffffffffu, pend)) >= DEFER_AT;
+            if (flush && pend) {
+              const u32 idx = find_or_claim(pkey);
+              if (idx != 0xFFFFFFFFu) update(idx, pmeta);
+              pend = false;
+            }
+            if (miss) {
+#pragma unroll
+              for (int i = 0; i < KW; i++) pkey[i] = key[i];
+              pmeta = meta;
+              pend = true;
+            }
+          } else if (miss) {
+            const u32 idx = find_or_claim(key);
+            if (idx != 0xFFFFFFFFu) update(idx, meta);
           }
         }
         const bool stop = __any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0);  // also orders this chunk's reads of the
@@ -642,7 +681,7 @@ __global__ void __launch_bounds__(256) build_items_kernel(const BuildArgs a) {
     it.sub = 0;
     it.nsub = 1;
     it.heavy = nsup > a.heavy_thr ? 1u : 0u;
-    it.pad = 0;
+    it.ninst = (u32)min(ri + ci, (u64)0xFFFFFFFFull);
     a.items[p] = it;
     if (nsup > 0xFFFFFFF0ull) a.counters[CTR_ERR] = 2;  // a partition this large cannot be indexed: more partitions needed
     if (it.heavy) {
