@@ -53,6 +53,21 @@ struct Pending {
   bool is_ctg = false;
 };
 
+// The parse stage runs as a two-slot pipeline: batch i is parsed (ALU-bound) on one slot's stream while the records of
+// batch i-1 are still being scattered (memory-bound) by the fill kernel on the other slot's stream. Each slot owns the
+// buffers that live from the parse kernel to the end of the fill kernel.
+struct ParseSlot {
+  cudaStream_t st = nullptr;
+  DevBuf d_cursor, d_tot, d_scan, d_elist, d_ecnt;
+  u64 *h_tot = nullptr;  // pinned: first record of every destination shard's range (+ total)
+  size_t h_tot_bytes = 0;
+  cudaEvent_t e0 = nullptr, ec = nullptr, ed = nullptr, e1 = nullptr;  // parse start / parse end / fill start / fill end
+  bool busy = false;   // a fill kernel was launched and its block has not been collected yet
+  Block blk;
+  size_t rec_bytes = 0;
+  std::vector<DevBuf> temps;  // inputs that must outlive the fill kernel (segment arrays)
+};
+
 }  // namespace
 
 struct kc_handle {
@@ -77,8 +92,12 @@ struct kc_handle {
   std::vector<Block> blocks;       // produced locally
   std::vector<Block> rblocks;      // received from peers (multi-shard)
   DevBuf stage_bytes[2], stage_offs[2];
-  DevBuf d_cursor, d_misc;  // d_misc: u64 instances, u32 err
-  DevBuf d_elist, d_ecnt;   // supermer lists of the batch being parsed (parse_kernel -> fill_kernel)
+  DevBuf d_misc;  // u64 instances, u32 err
+  ParseSlot slot[2];
+  u64 n_batches = 0;        // batches parsed so far: batch i uses slot i & 1
+  cudaEvent_t ev_blk = nullptr;  // "records of the block being handed to the exchange are written" (a slot's e1)
+  cudaEvent_t ev_first = nullptr;  // start of the first batch since the last drain (ms_parse = wall time of the stage)
+  bool stage_open = false;
   // outputs
   DevBuf out_keys, out_counts, out_left, out_right, pf_keys, pf_vals;
   u64 n_surv = 0, n_pf = 0;
@@ -317,8 +336,19 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
     CK(cudaEventCreateWithFlags(&h->ev_copy[i], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_free[i], cudaEventDisableTiming));
   }
+  CK(cudaEventCreate(&h->ev_first));
+  for (ParseSlot &sl : h->slot) {
+    CK(cudaStreamCreateWithFlags(&sl.st, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&sl.e0));
+    CK(cudaEventCreate(&sl.ec));
+    CK(cudaEventCreate(&sl.ed));
+    CK(cudaEventCreate(&sl.e1));
+    sl.h_tot_bytes = ((size_t)cfg->num_shards + 1) * 8;
+    CK(pin_get((void **)&sl.h_tot, sl.h_tot_bytes));
+  }
   RC(ensure(h, h->d_misc, 64));
   CK(cudaMemsetAsync(h->d_misc.p, 0, 64, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));
   h->pin_bytes = PIN_META + ((size_t)cfg->num_shards + 3) * (size_t)cfg->num_shards * 8;
   if ((size_t)(cfg->num_shards + 1) * 8 > PIN_META) return fail(h, KC_ERR_INVALID, "num_shards %d too large", cfg->num_shards);
   CK(pin_get((void **)&h->h_pin, h->pin_bytes));
@@ -459,15 +489,54 @@ int bucket_scan(kc_handle *h, const BucketHist *hist, u32 n, u64 *base, u32 P, u
   return cudaGetLastError() == cudaSuccess ? KC_OK : KC_ERR_CUDA;
 }
 
-// Parse one batch that is already on the device. `bytes` may be a virtual base (bytes + start always lands inside
-// the staged range). Either offsets (direct mode) or seg_* (segment mode) is given.
+// What a slot's last batch left behind: wait for its fill kernel, book its times, keep its block for the count stage.
+int collect_slot(kc_handle *h, ParseSlot &sl) {
+  if (!sl.busy) return KC_OK;
+  CK(cudaStreamSynchronize(sl.st));  // also surfaces kernel faults here
+  h->st.ms_parse_count += elapsed(sl.e0, sl.ec);
+  h->st.ms_parse_fill += elapsed(sl.ed, sl.e1);
+  h->st.supermers_out += sl.blk.tot_sup;
+  h->st.supermer_bytes_out += sl.rec_bytes;
+  h->blocks.push_back(std::move(sl.blk));
+  sl.blk = Block();
+  for (DevBuf &b : sl.temps) release(b);
+  sl.temps.clear();
+  sl.busy = false;
+  return KC_OK;
+}
+
+// End of a run of batches: both slots are collected; ms_parse gets the wall time of the run (the kernels of neighbouring
+// batches overlap, so it is less than the sum of the kernel times).
+int drain_parse(kc_handle *h) {
+  const int first = (int)(h->n_batches & 1);  // the older batch sits in the slot the next batch would take
+  cudaEvent_t last = nullptr;
+  for (int i = 0; i < 2; i++) {
+    ParseSlot &sl = h->slot[(first + i) & 1];
+    if (sl.busy) last = sl.e1;
+    RC(collect_slot(h, sl));
+  }
+  if (h->stage_open && last) h->st.ms_parse += elapsed(h->ev_first, last);
+  h->stage_open = false;
+  return KC_OK;
+}
+
+// Parse one batch that is already on the device (or will be once `in_ready` has happened). `bytes` may be a virtual base
+// (bytes + start always lands inside the staged range). Either offsets (direct mode) or seg_* (segment mode) is given.
+// Returns after the batch's fill kernel has been LAUNCHED: the input must stay valid until `consumed` (recorded behind the
+// fill kernel when given) or the next drain_parse. `temps`: device arrays the batch reads, released when it is collected.
 int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, const u64 *d_seg_start, const u32 *d_seg_len,
-                const uint16_t *d_seg_depth, u64 nseq, int max_len, bool ascii, bool is_ctg) {
+                const uint16_t *d_seg_depth, u64 nseq, int max_len, bool ascii, bool is_ctg, cudaEvent_t in_ready = nullptr,
+                cudaEvent_t consumed = nullptr, std::vector<DevBuf> *temps = nullptr) {
   if (nseq == 0) return KC_OK;
   const u32 NP = h->P * (u32)h->cfg.num_shards;
   const int N = h->cfg.num_shards;
-  RC(ensure(h, h->d_cursor, sizeof(u32) * NP));
-  RC(ensure(h, h->d_tot, sizeof(u64) * (size_t)(N + 1)));
+  ParseSlot &sl = h->slot[h->n_batches & 1];
+  RC(collect_slot(h, sl));  // the batch before last: long finished, this only books it
+  h->n_batches++;
+  cudaStream_t st = sl.st;
+  if (temps) sl.temps.swap(*temps);
+  RC(ensure(h, sl.d_cursor, sizeof(u32) * NP));
+  RC(ensure(h, sl.d_tot, sizeof(u64) * (size_t)(N + 1)));
   ParseArgs a;
   memset(&a, 0, sizeof(a));
   a.bytes = d_bytes;
@@ -508,49 +577,59 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   per_sm = std::max(per_sm, 1);
   per_sm_fill = std::max(per_sm_fill, 1);
   const u64 need_blocks = (nseq + threads - 1) / threads;
-  const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * per_sm * 2);
-  const unsigned grid_fill = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * per_sm_fill * 2);
+  // The two kernels of neighbouring batches share the SMs: each is launched with as many CTAs as fit HALF of an SM's slots
+  // (grid-stride loops), so that the other one's CTAs find room next to them (KC_PARSE_SHARE=0: each takes the whole SM)
+  static const int share = getenv("KC_PARSE_SHARE") ? atoi(getenv("KC_PARSE_SHARE")) : 1;
+  const int res_parse = share ? std::max(per_sm / 2, 1) : per_sm * 2, res_fill = share ? std::max(per_sm_fill / 2, 1) : per_sm_fill * 2;
+  const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * res_parse);
+  const unsigned grid_fill = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * res_fill);
   // supermer lists handed from the parse kernel to the fill kernel: one u32 per supermer, ecap slots per sequence
   if (NP >= (1u << 24)) return fail(h, KC_ERR_INVALID, "internal: %u buckets do not fit the 24-bit list entries", NP);
   a.ecap = std::max(1, max_len - a.k - 1);
-  RC(ensure(h, h->d_elist, need_blocks * (size_t)threads * (size_t)a.ecap * 4));
-  RC(ensure(h, h->d_ecnt, nseq));
-  a.elist = (u32 *)h->d_elist.p;
-  a.ecnt = (uint8_t *)h->d_ecnt.p;
+  RC(ensure(h, sl.d_elist, need_blocks * (size_t)threads * (size_t)a.ecap * 4));
+  RC(ensure(h, sl.d_ecnt, nseq));
+  a.elist = (u32 *)sl.d_elist.p;
+  a.ecnt = (uint8_t *)sl.d_ecnt.p;
 
-  cudaEvent_t e0 = h->ev_a, e1 = h->ev_b;
-  CK(cudaEventRecord(e0, h->s_main));
+  if (in_ready) CK(cudaStreamWaitEvent(st, in_ready, 0));
+  if (!h->stage_open) {
+    CK(cudaEventRecord(h->ev_first, st));
+    h->stage_open = true;
+  }
+  CK(cudaEventRecord(sl.e0, st));
   // parse_kernel: bucket histogram + supermer lists
   Block blk;
   blk.is_ctg = is_ctg;
   CK(dev_alloc((void **)&blk.d_hist, sizeof(BucketHist) * NP));
-  CK(cudaMemsetAsync(blk.d_hist, 0, sizeof(BucketHist) * NP, h->s_main));
+  CK(cudaMemsetAsync(blk.d_hist, 0, sizeof(BucketHist) * NP, st));
   a.hist = blk.d_hist;
-  k_count<<<grid, threads, smem, h->s_main>>>(a);
+  k_count<<<grid, threads, smem, st>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
-  CK(cudaEventRecord(h->ev_c, h->s_main));
+  CK(cudaEventRecord(sl.ec, st));
   // bucket layout on the device: the host only needs the totals (allocation size, the range that goes to each shard)
   CK(dev_alloc((void **)&blk.d_base, sizeof(u64) * ((size_t)NP + 1)));
-  RC(ensure(h, h->d_scan, sizeof(u64) * 1032));
-  RC(bucket_scan(h, blk.d_hist, NP, blk.d_base, h->P, (u64 *)h->d_tot.p, (u64 *)h->d_scan.p, h->s_main, (u32 *)h->d_cursor.p));
-  CK(cudaMemcpyAsync(h->h_pin, h->d_tot.p, sizeof(u64) * (size_t)(N + 1), cudaMemcpyDeviceToHost, h->s_main));
-  CK(cudaStreamSynchronize(h->s_main));
-  blk.dest_base.assign(h->h_pin, h->h_pin + N + 1);
+  RC(ensure(h, sl.d_scan, sizeof(u64) * 1032));
+  RC(bucket_scan(h, blk.d_hist, NP, blk.d_base, h->P, (u64 *)sl.d_tot.p, (u64 *)sl.d_scan.p, st, (u32 *)sl.d_cursor.p));
+  CK(cudaMemcpyAsync(sl.h_tot, sl.d_tot.p, sizeof(u64) * (size_t)(N + 1), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));  // the previous batch's fill kernel keeps running on the other slot's stream meanwhile
+  blk.dest_base.assign(sl.h_tot, sl.h_tot + N + 1);
   const u64 hs = blk.dest_base[N];
   blk.tot_sup = hs;
   if (hs == 0) {
-    CK(cudaEventRecord(e1, h->s_main));
     dev_free(blk.d_hist);
     dev_free(blk.d_base);
+    for (DevBuf &b : sl.temps) release(b);
+    sl.temps.clear();
+    if (consumed) CK(cudaEventRecord(consumed, st));
     return KC_OK;
   }
   const size_t rec_bytes = (size_t)hs * a.rw * 4;
   CK(dev_alloc((void **)&blk.rec, rec_bytes + 64));
   if (hs >> 32) return fail(h, KC_ERR_INVALID, "internal: %llu supermers in one batch do not fit the 32-bit bucket cursors", (unsigned long long)hs);
   // fill_kernel: records into the exact-size buckets
-  a.cursor = (u32 *)h->d_cursor.p;
+  a.cursor = (u32 *)sl.d_cursor.p;
   {
     static const int hint = getenv("KC_FILL_L2_HINT") ? atoi(getenv("KC_FILL_L2_HINT")) : 1;  // A/B switch (tools/prof_run.py)
     a.l2_hint = hint;
@@ -558,25 +637,22 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
     a.pair_lanes = pair;
   }
   a.rec = blk.rec;
-  CK(cudaEventRecord(h->ev_d, h->s_main));
-  k_fill<<<grid_fill, threads, smem_fill, h->s_main>>>(a);
+  CK(cudaEventRecord(sl.ed, st));
+  k_fill<<<grid_fill, threads, smem_fill, st>>>(a);
   h->st.gpu_launches++;
   h->st.n_parse_launches++;
   CK(cudaGetLastError());
-  CK(cudaEventRecord(e1, h->s_main));
-  CK(cudaEventRecord(h->ev_fill, h->s_main));
+  CK(cudaEventRecord(sl.e1, st));
+  if (consumed) CK(cudaEventRecord(consumed, st));
+  sl.blk = std::move(blk);
+  sl.rec_bytes = rec_bytes;
+  sl.busy = true;
   if (h->comm) {  // multi-shard with NCCL: this batch's supermers leave now, while the next batch is copied in and parsed
     h->phase_open = true;
-    int rcx = exchange_round(h, &blk, false, nullptr);
+    h->ev_blk = sl.e1;
+    int rcx = exchange_round(h, &sl.blk, false, nullptr);
     if (rcx) return rcx;
   }
-  CK(cudaStreamSynchronize(h->s_main));  // also surfaces kernel faults here
-  h->st.ms_parse += elapsed(e0, e1);
-  h->st.ms_parse_count += elapsed(e0, h->ev_c);
-  h->st.ms_parse_fill += elapsed(h->ev_d, e1);
-  h->st.supermers_out += hs;
-  h->st.supermer_bytes_out += rec_bytes;
-  h->blocks.push_back(std::move(blk));
   return KC_OK;
 }
 
@@ -592,12 +668,15 @@ extern "C" int kc_add_reads_device(kc_handle *h, const uint8_t *d_bytes, const u
   CK(cudaSetDevice(h->cfg.device));
   const u64 k1 = (u64)h->cfg.kmer_len + 1;
   decide_partitions(h, total_bytes > n_reads * k1 ? total_bytes - n_reads * k1 : 0);
-  const u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : h->comm ? (4ull << 20) : (8ull << 20);  // with peers: a batch is the unit that overlaps its exchange with the next parse
+  // a batch is the unit of overlap: its fill kernel runs beside the next batch's parse kernel, its exchange behind both
+  static const u64 def_batch = getenv("KC_BATCH_READS") ? (u64)atoll(getenv("KC_BATCH_READS")) : (2ull << 20);
+  const u64 batch = h->cfg.batch_reads > 0 ? (u64)h->cfg.batch_reads : def_batch;
   for (u64 r0 = 0; r0 < n_reads; r0 += batch) {
     const u64 n = std::min<u64>(batch, n_reads - r0);
     int rc = parse_batch(h, d_bytes, (const u64 *)d_offsets + r0, nullptr, nullptr, nullptr, n, (int)max_read_len, false, false);
     if (rc) return rc;
   }
+  RC(drain_parse(h));  // the caller owns the input again when this returns
   h->st.num_seqs += n_reads;
   h->st.num_bases += total_bytes;
   return KC_OK;
@@ -622,27 +701,29 @@ void tile_sequence(u64 start, u64 len, int k, int tile, uint16_t depth, std::vec
   }
 }
 
-// copy host arrays of segments to the device and parse them
+// copy host arrays of segments to the device and parse them (the arrays live until the batch is collected)
 int parse_segments(kc_handle *h, const uint8_t *d_bytes_virtual, std::vector<u64> &ss, std::vector<u32> &sl, std::vector<uint16_t> &sd,
-                   int max_len, bool ascii, bool is_ctg) {
+                   int max_len, bool ascii, bool is_ctg, cudaEvent_t in_ready = nullptr, cudaEvent_t consumed = nullptr) {
   const u64 n = ss.size();
   if (!n) return KC_OK;
-  DevBuf b0, b1, b2;
-  int rc = ensure(h, b0, n * 8);
-  if (!rc) rc = ensure(h, b1, n * 4);
-  if (!rc) rc = ensure(h, b2, n * 2);
-  if (!rc) {
-    cudaMemcpyAsync(b0.p, ss.data(), n * 8, cudaMemcpyHostToDevice, h->s_main);
-    cudaMemcpyAsync(b1.p, sl.data(), n * 4, cudaMemcpyHostToDevice, h->s_main);
-    cudaMemcpyAsync(b2.p, sd.data(), n * 2, cudaMemcpyHostToDevice, h->s_main);
-    rc = parse_batch(h, d_bytes_virtual, nullptr, (const u64 *)b0.p, (const u32 *)b1.p, (const uint16_t *)b2.p, n, max_len, ascii,
-                     is_ctg);
+  std::vector<DevBuf> t(3);
+  int rc = ensure(h, t[0], n * 8);
+  if (!rc) rc = ensure(h, t[1], n * 4);
+  if (!rc) rc = ensure(h, t[2], n * 2);
+  if (rc) {
+    for (DevBuf &b : t) release(b);
+    return rc;
   }
-  cudaStreamSynchronize(h->s_main);
-  release(b0);
-  release(b1);
-  release(b2);
-  return rc;
+  // pageable sources: these copies return once the source has been staged; the slot's stream orders them before its kernels
+  cudaStream_t st = h->slot[h->n_batches & 1].st;
+  RC(collect_slot(h, h->slot[h->n_batches & 1]));  // the stream must be done with the batch before last
+  cudaMemcpyAsync(t[0].p, ss.data(), n * 8, cudaMemcpyHostToDevice, st);
+  cudaMemcpyAsync(t[1].p, sl.data(), n * 4, cudaMemcpyHostToDevice, st);
+  cudaMemcpyAsync(t[2].p, sd.data(), n * 2, cudaMemcpyHostToDevice, st);
+  const u64 *p0 = (const u64 *)t[0].p;
+  const u32 *p1 = (const u32 *)t[1].p;
+  const uint16_t *p2 = (const uint16_t *)t[2].p;
+  return parse_batch(h, d_bytes_virtual, nullptr, p0, p1, p2, n, max_len, ascii, is_ctg, in_ready, consumed, &t);
 }
 
 }  // namespace
@@ -662,23 +743,25 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
   const u64 avg = std::max<u64>(1, (offsets[n_reads] - offsets[0]) / n_reads);
   batch = std::max<u64>(1, std::min<u64>(batch, (1ull << 30) / avg));  // <= ~1 GB of bases per batch
   const u64 nb = (n_reads + batch - 1) / batch;
-  cudaEvent_t t0[2], t1[2];
-  for (int i = 0; i < 2; i++) {
+  std::vector<cudaEvent_t> t0(nb), t1(nb);  // copy times, read once everything has drained
+  for (u64 i = 0; i < nb; i++) {
     CK(cudaEventCreate(&t0[i]));
     CK(cudaEventCreate(&t1[i]));
   }
-  float ms_copy = 0;
+  // two staging buffers: the copy of batch i+1 overlaps the parse of batch i; a buffer is overwritten only after the FILL
+  // kernel of the batch that used it (it reads the bases again), which the copy stream waits for on the device
   auto issue_copy = [&](u64 bi) -> int {
     const int sl = (int)(bi & 1);
     const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
     const u64 b0 = offsets[r0], b1 = offsets[r1];
-    CK(cudaEventSynchronize(h->ev_free[sl]));  // the parse that last used this stage has finished
+    if (h->stage_bytes[sl].bytes < b1 - b0 + 64 || h->stage_offs[sl].bytes < (r1 - r0 + 1) * 8) RC(drain_parse(h));  // about to reallocate
     RC(ensure(h, h->stage_bytes[sl], b1 - b0 + 64));
     RC(ensure(h, h->stage_offs[sl], (r1 - r0 + 1) * 8));
-    CK(cudaEventRecord(t0[sl], h->s_copy));
+    CK(cudaStreamWaitEvent(h->s_copy, h->ev_free[sl], 0));
+    CK(cudaEventRecord(t0[bi], h->s_copy));
     CK(cudaMemcpyAsync(h->stage_bytes[sl].p, bytes + b0, b1 - b0, cudaMemcpyHostToDevice, h->s_copy));
     CK(cudaMemcpyAsync(h->stage_offs[sl].p, offsets + r0, (r1 - r0 + 1) * 8, cudaMemcpyHostToDevice, h->s_copy));
-    CK(cudaEventRecord(t1[sl], h->s_copy));
+    CK(cudaEventRecord(t1[bi], h->s_copy));
     CK(cudaEventRecord(h->ev_copy[sl], h->s_copy));
     return KC_OK;
   };
@@ -687,7 +770,7 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
   for (u64 bi = 0; bi < nb; bi++) {
     const int sl = (int)(bi & 1);
     const u64 r0 = bi * batch, r1 = std::min<u64>(n_reads, r0 + batch);
-    if (bi + 1 < nb) {  // next batch's copy overlaps this batch's parse
+    if (bi + 1 < nb) {  // the next batch's copy runs while this batch is parsed
       rc = issue_copy(bi + 1);
       if (rc) return rc;
     }
@@ -695,21 +778,24 @@ extern "C" int kc_add_reads(kc_handle *h, const uint8_t *bytes, const uint64_t *
     u64 max_len = 0;  // scanned while the copies are in flight
     for (u64 r = r0; r < r1; r++) max_len = std::max<u64>(max_len, offsets[r + 1] - offsets[r]);
     const bool tiled = max_len > (u64)SEG_MAX;
-    CK(cudaEventSynchronize(h->ev_copy[sl]));
-    ms_copy += elapsed(t0[sl], t1[sl]);
     if (!tiled) {
-      rc = parse_batch(h, vbase, (const u64 *)h->stage_offs[sl].p, nullptr, nullptr, nullptr, r1 - r0, (int)max_len, false, false);
+      rc = parse_batch(h, vbase, (const u64 *)h->stage_offs[sl].p, nullptr, nullptr, nullptr, r1 - r0, (int)max_len, false, false,
+                       h->ev_copy[sl], h->ev_free[sl]);
     } else {
       std::vector<u64> ss;
       std::vector<u32> sl2;
       std::vector<uint16_t> sd;
       for (u64 r = r0; r < r1; r++) tile_sequence(offsets[r], offsets[r + 1] - offsets[r], k, SEG_MAX, 1, ss, sl2, sd);
-      rc = parse_segments(h, vbase, ss, sl2, sd, SEG_MAX, false, false);
+      if (ss.empty()) CK(cudaEventRecord(h->ev_free[sl], h->s_copy));  // nothing reads this stage
+      rc = parse_segments(h, vbase, ss, sl2, sd, SEG_MAX, false, false, h->ev_copy[sl], h->ev_free[sl]);
     }
     if (rc) return rc;
-    CK(cudaEventRecord(h->ev_free[sl], h->s_main));
   }
-  for (int i = 0; i < 2; i++) {
+  RC(drain_parse(h));
+  CK(cudaStreamSynchronize(h->s_copy));
+  float ms_copy = 0;
+  for (u64 i = 0; i < nb; i++) {
+    ms_copy += elapsed(t0[i], t1[i]);
     cudaEventDestroy(t0[i]);
     cudaEventDestroy(t1[i]);
   }
@@ -929,19 +1015,20 @@ extern "C" int kc_add_reads_resident(kc_handle *h, kc_reads *r) {
   decide_partitions(h, r->total_bytes > r->n_reads * k1 ? r->total_bytes - r->n_reads * k1 : 0);
   for (u64 bi = 0; bi < r->ready.size(); bi++) {
     const u64 r0 = bi * r->batch, r1 = std::min<u64>(r->n_reads, r0 + r->batch);
-    CK(cudaStreamWaitEvent(h->s_main, r->ready[bi], 0));  // first use right after kc_reads_create overlaps the upload
-    int rc;
+    int rc;  // batches wait for their upload on the device: first use right after kc_reads_create overlaps the upload
     if (r->max_len[bi] <= (u32)SEG_MAX) {
-      rc = parse_batch(h, r->d_bytes, r->d_offsets + r0, nullptr, nullptr, nullptr, r1 - r0, (int)r->max_len[bi], false, false);
+      rc = parse_batch(h, r->d_bytes, r->d_offsets + r0, nullptr, nullptr, nullptr, r1 - r0, (int)r->max_len[bi], false, false,
+                       r->ready[bi]);
     } else {
       std::vector<u64> ss;
       std::vector<u32> sl;
       std::vector<uint16_t> sd;
       for (u64 i = r0; i < r1; i++) tile_sequence(r->h_offsets[i], r->h_offsets[i + 1] - r->h_offsets[i], k, SEG_MAX, 1, ss, sl, sd);
-      rc = parse_segments(h, r->d_bytes, ss, sl, sd, SEG_MAX, false, false);
+      rc = parse_segments(h, r->d_bytes, ss, sl, sd, SEG_MAX, false, false, r->ready[bi]);
     }
     if (rc) return rc;
   }
+  RC(drain_parse(h));
   h->st.num_seqs += r->n_reads;
   h->st.num_bases += r->total_bytes;
   if (int rcx = reads_check(r)) return fail(h, rcx, "kc_reads_create_fastq: illegal base character in the reads (packed_reads.cpp:104)");
@@ -982,8 +1069,9 @@ int add_ascii(kc_handle *h, const char *seqs, const uint64_t *offsets, const dou
   int rc = ensure(h, d_seq, b1 - b0 + 64);
   if (rc) return rc;
   CK(cudaMemcpyAsync(d_seq.p, seqs + b0, b1 - b0, cudaMemcpyHostToDevice, h->s_main));
+  CK(cudaStreamSynchronize(h->s_main));  // the parse slots' streams read it
   // segments are parsed in slices so that the per-batch bucket buffers stay bounded
-  const size_t SLICE = 4u << 20;
+  const size_t SLICE = 2u << 20;
   for (size_t s0 = 0; s0 < ss.size() && !rc; s0 += SLICE) {
     const size_t s1 = std::min(ss.size(), s0 + SLICE);
     std::vector<u64> a(ss.begin() + s0, ss.begin() + s1);
@@ -991,7 +1079,10 @@ int add_ascii(kc_handle *h, const char *seqs, const uint64_t *offsets, const dou
     std::vector<uint16_t> c(sd.begin() + s0, sd.begin() + s1);
     rc = parse_segments(h, (const uint8_t *)d_seq.p - b0, a, b, c, SEG_MAX, true, is_ctg);
   }
-  CK(cudaStreamSynchronize(h->s_main));
+  {
+    const int rcd = drain_parse(h);
+    if (!rc) rc = rcd;
+  }
   release(d_seq);
   if (rc) return rc;
   u32 err = 0;
@@ -1692,7 +1783,18 @@ extern "C" int kc_destroy(kc_handle *h) {
   if (h->s_comm) cudaStreamSynchronize(h->s_comm);
   for (auto &b : h->blocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   for (auto &b : h->rblocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
-  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_cursor, &h->d_elist, &h->d_ecnt, &h->d_meta, &h->d_meta_all,
+  for (ParseSlot &sl : h->slot) {
+    if (sl.st) cudaStreamSynchronize(sl.st);
+    if (sl.busy) { dev_free(sl.blk.rec); dev_free(sl.blk.d_hist); dev_free(sl.blk.d_base); }
+    for (DevBuf &b : sl.temps) release(b);
+    for (DevBuf *b : {&sl.d_cursor, &sl.d_tot, &sl.d_scan, &sl.d_elist, &sl.d_ecnt}) release(*b);
+    for (cudaEvent_t e : {sl.e0, sl.ec, sl.ed, sl.e1})
+      if (e) cudaEventDestroy(e);
+    if (sl.st) cudaStreamDestroy(sl.st);
+    pin_put(sl.h_tot, sl.h_tot_bytes);
+  }
+  if (h->ev_first) cudaEventDestroy(h->ev_first);
+  DevBuf *bufs[] = {&h->stage_bytes[0], &h->stage_bytes[1], &h->stage_offs[0], &h->stage_offs[1], &h->d_meta, &h->d_meta_all,
                     &h->d_tot, &h->d_scan, &h->d_scan_comm, &h->d_misc, &h->out_keys, &h->out_counts, &h->out_left, &h->out_right,
                     &h->pf_keys, &h->pf_vals};
   for (DevBuf *b : bufs) release(*b);

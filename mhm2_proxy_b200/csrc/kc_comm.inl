@@ -254,7 +254,7 @@ int exchange_round(kc_handle *h, const Block *blk, bool done, bool *all_done) {
   bool any_send = false;
   for (int d = 0; d < N; d++) any_send = any_send || mine[3 + d] != 0;
   if (inc.empty() && !any_send) return KC_OK;
-  if (any_send) CK(cudaStreamWaitEvent(st, h->ev_fill, 0));  // the records are being written by the fill kernel on the main stream
+  if (any_send) CK(cudaStreamWaitEvent(st, h->ev_blk, 0));  // the records are being written by the fill kernel on a parse slot's stream
   std::pair<cudaEvent_t, cudaEvent_t> ev;  // what the group occupies on the communication stream: ms_comm
   CK(cudaEventCreate(&ev.first));
   CK(cudaEventCreate(&ev.second));

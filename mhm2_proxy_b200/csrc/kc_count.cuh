@@ -127,6 +127,9 @@ __device__ __forceinline__ u64 lds64_volatile(u32 a) {
   asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(v) : "r"(a) : "memory");
   return v;
 }
+__device__ __forceinline__ void sts16(u32 a, u32 v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory");
+}
 __device__ __forceinline__ void atoms_add(u32 a, u32 v) {  // shared-space address; no result wanted (RED-style)
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
@@ -270,20 +273,6 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         }
         __syncwarp();
 
-        // ---- c. every k-mer instance of the chunk ----
-        // Fast path (about 7 of 8 instances at 33x coverage): extract, hash, ONE 128-bit bucket load, key compare, two counter
-        // adds. A miss (new key, shared fingerprint, full bucket) needs the probe-and-claim path, ~70 instructions that ran
-        // with 4 of 32 lanes active when every lane handled its own miss at once. Misses are therefore DEFERRED: the lane
-        // parks (key, slots) in registers and goes on; the warp runs the slow path only when a lane with a parked miss misses
-        // again or DEFER_AT lanes are waiting, i.e. every third or fourth iteration with a dozen lanes active. Counter
-        // updates commute, so the order of inserts is free. (KW >= 3: a parked key would cost 6-8 registers; not deferred.)
-        constexpr bool DEFER = KW <= 2;
-        constexpr u32 DEFER_AT = 20;
-        bool pend = false;
-        u64 pkey[KW];
-        u32 pmeta = 0;
-#pragma unroll
-        for (int i = 0; i < KW; i++) pkey[i] = 0;
         // counters of dense entry idx: meta = left slot | right slot << 3 | (contigs) header bits 15..31
         auto update = [&](u32 idx, u32 meta) {
           const u32 sl = meta & 7u, sr = (meta >> 3) & 7u;
@@ -379,16 +368,23 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           my_max_probe = max(my_max_probe, probes);
           return idx;
         };
-        // one more (empty) iteration after the last instance flushes what is still parked
-        for (u32 t0 = 0; t0 < total + (DEFER ? GRP_THREADS : 0u); t0 += GRP_THREADS) {
+        // ---- c. every k-mer instance of the chunk ----
+        // Pass 1, the fast path (about 5 of 6 instances at 33x coverage): extract, hash, ONE 128-bit bucket load, key compare,
+        // two counter adds. An instance that misses (new key, shared fingerprint, key that lives in a neighbouring bucket)
+        // needs the probe-and-claim path; handled where it occurs that path ran with 4-8 of 32 lanes active in almost every
+        // iteration (a quarter of all instructions). Instead the instance's LIST ENTRY is compacted to the front of the list
+        // (over entries already consumed), and pass 2 walks those entries with all lanes: extracting a k-mer again costs less
+        // than a third of one divergent pass through the slow path. Counter updates commute, so the order is free.
+        u32 nmiss = 0;
+        for (u32 t0 = 0; t0 < total; t0 += GRP_THREADS) {
           const u32 t = t0 + (u32)gt;
           bool miss = false;
-          u64 key[KW];
-          u32 meta = 0;
+          u32 e = 0;
           if (t < total) {
-            const u32 e = lds16(expl_s + 2u * t);
+            e = lds16(expl_s + 2u * t);
             const u32 si = e & 255u;
             const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
+            u64 key[KW];
             Instance in;
             u32 hdr = 0u;
             if (KC) {
@@ -400,7 +396,6 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
               if (CTG) hdr = rec[0];
               in = extract_any<KW>(rec, j, k, nwb, key);
             }
-            meta = in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u);
             const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
             if (it.nsub <= 1 || ((u32)(h >> 40) & (it.nsub - 1)) == it.sub) {
               // find: one 128-bit load of the bucket. entry ^ fp is (dense index + 1) <= IDX_MASK exactly when the entry's upper
@@ -417,28 +412,39 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
                 for (int i = 0; i < KW; i++) same = same && (lds64_volatile(ka + 8u * i) == key[i]);
                 if (same) {
                   miss = false;
-                  update(mn - 1u, meta);
+                  update(mn - 1u, in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u));
                 }
               }
             }
           }
-          if (DEFER) {
-            const bool flush = __any_sync(0xffffffffu, miss && pend) || t0 >= total ||
-                               (u32)__popc(__ballot_sync(0xffffffffu, pend)) >= DEFER_AT;
-            if (flush && pend) {
-              const u32 idx = find_or_claim(pkey);
-              if (idx != 0xFFFFFFFFu) update(idx, pmeta);
-              pend = false;
+          const u32 mm = __ballot_sync(0xffffffffu, miss);
+          if (mm) {  // entries [0, nmiss) are behind the read position: nmiss <= t0
+            if (miss) sts16(expl_s + 2u * (nmiss + (u32)__popc(mm & ((1u << gt) - 1u))), e);
+            nmiss += (u32)__popc(mm);
+          }
+        }
+        __syncwarp();
+        // pass 2: the misses, all lanes busy
+        for (u32 t0 = 0; t0 < nmiss; t0 += GRP_THREADS) {
+          const u32 t = t0 + (u32)gt;
+          if (t < nmiss) {
+            const u32 e = lds16(expl_s + 2u * t);
+            const u32 si = e & 255u;
+            const int j = (int)(e >> 8) + 1;
+            u64 key[KW];
+            Instance in;
+            u32 hdr = 0u;
+            if (KC) {
+              const u32 rec_s = stage_s + si * (u32)(rw * 4);
+              if (CTG) hdr = lds32(rec_s);
+              in = extract_fixed<KW, KC ? KC : 21>(rec_s, j, key);
+            } else {
+              const u32 *rec = stage + si * rw;
+              if (CTG) hdr = rec[0];
+              in = extract_any<KW>(rec, j, k, nwb, key);
             }
-            if (miss) {
-#pragma unroll
-              for (int i = 0; i < KW; i++) pkey[i] = key[i];
-              pmeta = meta;
-              pend = true;
-            }
-          } else if (miss) {
             const u32 idx = find_or_claim(key);
-            if (idx != 0xFFFFFFFFu) update(idx, meta);
+            if (idx != 0xFFFFFFFFu) update(idx, in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u));
           }
         }
         const bool stop = __any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0);  // also orders this chunk's reads of the
