@@ -577,9 +577,10 @@ int parse_batch(kc_handle *h, const uint8_t *d_bytes, const u64 *d_offsets, cons
   per_sm = std::max(per_sm, 1);
   per_sm_fill = std::max(per_sm_fill, 1);
   const u64 need_blocks = (nseq + threads - 1) / threads;
-  // The two kernels of neighbouring batches share the SMs: each is launched with as many CTAs as fit HALF of an SM's slots
-  // (grid-stride loops), so that the other one's CTAs find room next to them (KC_PARSE_SHARE=0: each takes the whole SM)
-  static const int share = getenv("KC_PARSE_SHARE") ? atoi(getenv("KC_PARSE_SHARE")) : 1;
+  // The kernels of neighbouring batches overlap where one leaves SM slots free (tails, the memory-bound fill kernel's
+  // stalls). Measured on C2 (r2_v2 A/B): full-size grids 79.5 ms per step, grids of half an SM's slots each
+  // (KC_PARSE_SHARE=1) 95.9 ms — the ALU-bound parse kernel needs all its warps; so full-size grids are the default.
+  static const int share = getenv("KC_PARSE_SHARE") ? atoi(getenv("KC_PARSE_SHARE")) : 0;
   const int res_parse = share ? std::max(per_sm / 2, 1) : per_sm * 2, res_fill = share ? std::max(per_sm_fill / 2, 1) : per_sm_fill * 2;
   const unsigned grid = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * res_parse);
   const unsigned grid_fill = (unsigned)std::min<u64>(need_blocks, (u64)h->sms * res_fill);
