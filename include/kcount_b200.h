@@ -179,6 +179,22 @@ int kc_dump_kmers(kc_handle *h, const char *path);
  * the same digest of the reference's local_kmers at full workload size. */
 int kc_table_digest(kc_handle *h, uint64_t out4[4]);
 
+/* No counterpart in the reference: added for callers that cannot allocate (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). The same digest as kc_table_digest over a table
+ * the caller holds in DEVICE memory on `device` (e.g. the arrays of kc_survivors_device): n rows of n_longs key words, u16
+ * counts, left and right chars; d_out4 (DEVICE memory, 4 x u64) receives {n, sum of counts, sum of mix, xor of mix}.
+ * The call enqueues one 256-byte memset and ONE kernel on cuda_stream (a cudaStream_t; NULL = the default stream) and
+ * returns without synchronising; it calls no cudaMalloc / cudaFree and no allocating library routine. Its scratch (one partial
+ * result per CTA + a ticket) is a file-scope __device__ array of 128.25 KB that every GPU loading the library holds until
+ * exit. LIMIT: n <= KC_DIGEST_STATIC_MAX_ROWS (2^28 rows = 4096 CTAs x 65536 rows); more is rejected with KC_ERR_INVALID and a
+ * message in errbuf (optional, errbuf_len bytes). All calls on one device share the scratch: calls that overlap on the GPU
+ * (different streams, no ordering between them) race — order them. The first call per device looks the array's address up
+ * (cudaGetSymbolAddress): make it once before starting a stream capture. */
+#define KC_DIGEST_STATIC_MAX_ROWS 268435456ull
+int kc_table_digest_static(int32_t device, const uint64_t *d_kmer_words, const uint16_t *d_counts, const char *d_left,
+                           const char *d_right, uint64_t n, int32_t n_longs, uint64_t *d_out4, void *cuda_stream, char *errbuf,
+                           uint64_t errbuf_len);
+
 /* device-resident view of the same arrays (valid until kc_destroy) */
 int kc_survivors_device(kc_handle *h, const uint64_t **d_kmer_words, const uint16_t **d_counts, const char **d_left,
                         const char **d_right);

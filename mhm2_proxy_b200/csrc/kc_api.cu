@@ -1934,4 +1934,124 @@ done:
   return rc;
 }
 
+// ---------------------------------------------------------------- allocation-free digest ----------
+// kc_table_digest_static: the digest of kc_table_digest for callers that cannot allocate (CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc). No counterpart in the reference. Its scratch — one partial result per CTA and a
+// ticket — lives in a file-scope __device__ array that every GPU loading this library holds until exit
+// (KC_DIGEST_STATIC_BLOCKS * 32 + 256 bytes = 128.25 KB). In host code the array's NAME is only a host-side stand-in: the
+// device address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+namespace {
+constexpr u32 KC_DIGEST_STATIC_BLOCKS = 4096;        // partial results the scratch array holds
+constexpr u32 KC_DIGEST_STATIC_ROWS_PER_BLOCK = 65536;
+static_assert((u64)KC_DIGEST_STATIC_BLOCKS * KC_DIGEST_STATIC_ROWS_PER_BLOCK == KC_DIGEST_STATIC_MAX_ROWS, "header and scratch size agree");
+// [0, 32): ticket (must be zero when a launch starts) + padding; then 4 words per CTA
+static __device__ __align__(256) unsigned long long kc_digest_scratch[32 + 4 * KC_DIGEST_STATIC_BLOCKS];
+
+__global__ void __launch_bounds__(256) digest_static_kernel(const u64 *keys, const uint16_t *counts, const char *left, const char *right,
+                                                            u64 n, int KW, unsigned long long *scratch, u64 *out4) {
+  __shared__ u64 sh[3][8];
+  __shared__ bool s_last;
+  const u64 r0 = (u64)blockIdx.x * KC_DIGEST_STATIC_ROWS_PER_BLOCK;
+  const u64 r1 = r0 + KC_DIGEST_STATIC_ROWS_PER_BLOCK < n ? r0 + KC_DIGEST_STATIC_ROWS_PER_BLOCK : n;
+  u64 sc = 0, sm = 0, xm = 0;
+  for (u64 i = r0 + threadIdx.x; i < r1; i += blockDim.x) {
+    u64 x = 0x9E3779B97F4A7C15ULL;
+    for (int j = 0; j < KW; j++) x = fmix64(x ^ keys[i * KW + j]);
+    const u64 c = counts[i];
+    x = fmix64(x ^ (c | ((u64)(unsigned char)left[i] << 16) | ((u64)(unsigned char)right[i] << 24)));
+    sc += c;
+    sm += x;
+    xm ^= x;
+  }
+  auto block_reduce = [&](u64 &a, u64 &b, u64 &c) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, d);
+      b += __shfl_xor_sync(0xffffffffu, b, d);
+      c ^= __shfl_xor_sync(0xffffffffu, c, d);
+    }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) { sh[0][wid] = a; sh[1][wid] = b; sh[2][wid] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int w = 1; w < 8; w++) { a += sh[0][w]; b += sh[1][w]; c ^= sh[2][w]; }
+    }
+  };
+  block_reduce(sc, sm, xm);
+  unsigned long long *part = scratch + 32;
+  if (threadIdx.x == 0) {
+    part[4 * blockIdx.x + 1] = sc;
+    part[4 * blockIdx.x + 2] = sm;
+    part[4 * blockIdx.x + 3] = xm;
+    __threadfence();
+    s_last = atomicAdd(&scratch[0], 1ull) == (unsigned long long)gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  sc = sm = xm = 0;
+  for (u32 b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+    sc += ((volatile unsigned long long *)part)[4 * b + 1];
+    sm += ((volatile unsigned long long *)part)[4 * b + 2];
+    xm ^= ((volatile unsigned long long *)part)[4 * b + 3];
+  }
+  block_reduce(sc, sm, xm);
+  if (threadIdx.x == 0) {
+    out4[0] = n;
+    out4[1] = sc;
+    out4[2] = sm;
+    out4[3] = xm;
+    scratch[0] = 0;  // leave the ticket as the next call needs it (the call clears it as well)
+  }
+}
+
+constexpr int KC_MAX_DEVICES = 64;
+std::mutex g_digest_static_mu;
+unsigned long long *g_digest_static_ptr[KC_MAX_DEVICES];  // device address of kc_digest_scratch on each device
+}  // namespace
+
+extern "C" int kc_table_digest_static(int32_t device, const uint64_t *d_kmer_words, const uint16_t *d_counts, const char *d_left,
+                                      const char *d_right, uint64_t n, int32_t n_longs, uint64_t *d_out4, void *cuda_stream,
+                                      char *errbuf, uint64_t errbuf_len) {
+  auto say = [&](int code, const char *fmt, ...) {
+    if (errbuf && errbuf_len) {
+      va_list ap;
+      va_start(ap, fmt);
+      vsnprintf(errbuf, (size_t)errbuf_len, fmt, ap);
+      va_end(ap);
+    }
+    return code;
+  };
+  if (errbuf && errbuf_len) errbuf[0] = 0;
+  if (device < 0 || device >= KC_MAX_DEVICES) return say(KC_ERR_INVALID, "device %d outside 0..%d", device, KC_MAX_DEVICES - 1);
+  if (n_longs < 1 || n_longs > 4) return say(KC_ERR_INVALID, "n_longs %d outside 1..4", n_longs);
+  if (!d_out4 || (n && (!d_kmer_words || !d_counts || !d_left || !d_right))) return say(KC_ERR_INVALID, "null pointer");
+  if (n > KC_DIGEST_STATIC_MAX_ROWS)
+    return say(KC_ERR_INVALID, "%llu rows exceed the static scratch's limit of %llu rows (KC_DIGEST_STATIC_MAX_ROWS): use kc_table_digest",
+               (unsigned long long)n, (unsigned long long)KC_DIGEST_STATIC_MAX_ROWS);
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return say(KC_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  unsigned long long *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_digest_static_mu);
+    if (!g_digest_static_ptr[device]) {  // set-up, once per device, with that device current
+      void *p = nullptr;
+      e = cudaGetSymbolAddress(&p, kc_digest_scratch);
+      if (e != cudaSuccess || !p) return say(KC_ERR_CUDA, "cudaGetSymbolAddress(kc_digest_scratch): %s", cudaGetErrorString(e));
+      g_digest_static_ptr[device] = (unsigned long long *)p;
+    }
+    scratch = g_digest_static_ptr[device];
+  }
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  // the array keeps the last call's contents: the ticket must start at zero (partials are overwritten before they are read)
+  e = cudaMemsetAsync(scratch, 0, 256, st);
+  if (e != cudaSuccess) return say(KC_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+  const unsigned grid = (unsigned)std::max<u64>(1, (n + KC_DIGEST_STATIC_ROWS_PER_BLOCK - 1) / KC_DIGEST_STATIC_ROWS_PER_BLOCK);
+  digest_static_kernel<<<grid, 256, 0, st>>>((const u64 *)d_kmer_words, d_counts, d_left, d_right, n, n_longs, scratch, (u64 *)d_out4);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return say(KC_ERR_CUDA, "digest_static_kernel launch: %s", cudaGetErrorString(e));
+  return KC_OK;
+}
+
 #include "kc_comm.inl"

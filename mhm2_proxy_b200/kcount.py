@@ -40,6 +40,7 @@ EXPORTS = [
     "kc_comm_unique_id", "kc_comm_init", "kc_finish", "kc_finish_to_host", "kc_finish_local_group", "kc_num_survivors", "kc_copy_survivors", "kc_survivors_device",
     "kc_num_prefilter", "kc_copy_prefilter", "kc_get_stats", "kc_prim_kmers", "kc_prim_get_ext",
     "kc_flush", "kc_device_count", "kc_table_digest", "kc_debug_set_key_cap", "kc_struct_sizes",
+    "kc_table_digest_static",
 ]
 
 _lib = None
@@ -89,6 +90,7 @@ def load_library():
     lib.kc_device_count.argtypes = [C.POINTER(i32)]
     lib.kc_table_digest.argtypes = [vp, vp]
     lib.kc_debug_set_key_cap.argtypes = [vp, i32]
+    lib.kc_table_digest_static.argtypes = [i32, vp, vp, vp, vp, u64, i32, vp, vp, C.c_char_p, u64]
     lib.kc_struct_sizes.argtypes = [C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.kc_struct_sizes.restype = None
     a, b = C.c_uint32(), C.c_uint32()
@@ -350,6 +352,20 @@ def table_digest(keys, counts, left, right):
         x = _fmix64(x ^ (c | (np.asarray(left).astype(np.uint64) << np.uint64(16)) | (np.asarray(right).astype(np.uint64) << np.uint64(24))))
         sm = int(x.sum(dtype=np.uint64)) if len(x) else 0
     return (len(counts), int(c.sum()), sm, int(np.bitwise_xor.reduce(x)) if len(x) else 0)
+
+
+DIGEST_STATIC_MAX_ROWS = 1 << 28
+
+
+def table_digest_static(device, d_keys, d_counts, d_left, d_right, n, n_longs, d_out4, stream=0):
+    """kc_table_digest_static: allocation-free digest of a table in DEVICE memory (raw pointers); the result lands in the
+    4 x u64 DEVICE buffer d_out4 once the stream has run. Raises KcountError with the library's message on rejection."""
+    lib = load_library()
+    err = C.create_string_buffer(256)
+    rc = lib.kc_table_digest_static(device, C.c_void_p(d_keys), C.c_void_p(d_counts), C.c_void_p(d_left), C.c_void_p(d_right), n,
+                                    n_longs, C.c_void_p(d_out4), C.c_void_p(stream), err, 256)
+    if rc != KC_OK:
+        raise KcountError(f"kc_table_digest_static failed ({ERR_NAMES.get(rc, rc)}): {err.value.decode()}")
 
 
 def device_count():
