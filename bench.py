@@ -234,9 +234,9 @@ def run_reference_arm(args):
 class HostOut:
     """Pinned host buffers that receive the surviving table in the end-to-end arm (allocated once, like an application would)."""
 
-    def __init__(self, n_reads, n_longs_max):
+    def __init__(self, rows, n_longs_max):
         import torch
-        self.cap = max(1 << 20, n_reads * 6)  # survivors are bounded by the distinct genomic k-mers, far below this
+        self.cap = max(1 << 20, int(rows))
         self.keys = torch.empty(self.cap * n_longs_max, dtype=torch.int64, pin_memory=True)
         self.counts = torch.empty(self.cap, dtype=torch.int16, pin_memory=True)
         self.left = torch.empty(self.cap, dtype=torch.uint8, pin_memory=True)
@@ -371,6 +371,7 @@ def dropin_seam(wl, ks):
     lib = C.CDLL(harness.DROPIN_SO)
     lib.odrop_time.restype = C.c_double
     lib.odrop_time.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.odrop_seam_seconds.argtypes = [C.c_void_p]
     rb = wl.tb.numpy()
     ro = wl.to.numpy().astype(np.uint64)
     secs, inst, per_k = 0.0, 0, {}
@@ -379,9 +380,14 @@ def dropin_seam(wl, ks):
         t = lib.odrop_time(k, 33, 2, rb.ctypes.data, ro.ctypes.data, wl.n_reads, nk.ctypes.data)
         if t < 0:
             return None
+        sp = np.zeros(3)
+        lib.odrop_seam_seconds(sp.ctypes.data_as(C.c_void_p))
         secs += t
         inst += wl.n_reads * (READ_LEN - k - 1)
-        per_k[str(k)] = {"seconds": round(t, 3), "local_kmers": int(nk[0])}
+        per_k[str(k)] = {"seconds": round(t, 3), "local_kmers": int(nk[0]),
+                         "seconds_reference_count_kmers_loop": round(t - float(sp.sum()), 3),  # PackedRead::unpack + tolower, one thread
+                         "seconds_binding_staging": round(float(sp[0]), 3), "seconds_inside_library": round(float(sp[1]), 3),
+                         "seconds_filling_local_kmers": round(float(sp[2]), 3)}
     return {"value": inst / secs, "unit": UNIT, "seconds": round(secs, 3), "per_k": per_k,
             "path": "reference analyze_kmers<MAX_K> (count_kmers unpacks every PackedRead to ASCII on one host thread, "
                     "SeqBlockInserter::process_seq stages it, kc_add_reads_ascii, kc_finish, survivors inserted one by one into "
@@ -417,7 +423,7 @@ def run_ours(args):
         d_b = wl.tb.cuda(non_blocking=True)
         d_o = wl.to.cuda(non_blocking=True)
         torch.cuda.synchronize()
-        hout = HostOut(wl.n_reads, max(k // 32 + 1 for k in wl.ks))
+        hout = None  # sized from the tables the device-resident passes produce (an application knows its genome size)
 
         def one_step(mode):
             """All k rounds over one set of reads. End-to-end mode: host -> device copy of the reads (once; HBM keeps them for
@@ -461,6 +467,7 @@ def run_ours(args):
         if with_parity and world > 1:  # before timing: the NCCL data plane must produce the reference's per-owner tables
             parity = parity_check(kcount, args, rank, world, local, wl, d_b, d_o, uid, dist)
         el, stats, clocks, wall = timed("device", steps, warmup, sampler)
+        hout = HostOut(1.1 * max(s["survivors"] for s in stats) + (1 << 20), max(k // 32 + 1 for k in wl.ks))
         el2, stats2, _, _ = timed("host", e2e_steps, e2e_warmup)
         # invariants of every timed pass, summed over ranks: nothing parsed may be missing from the tables
         sums = [sum(s["instances_parsed"] for s in stats), sum(s["instances_inserted"] for s in stats),

@@ -17,6 +17,7 @@
 //   * insert_into_local_hashtable runs exchange + count + filter on the GPU and drains the survivors into local_kmers.
 // This file contains no CUDA and includes no torch header: plain C++17 + the C ABI.
 #include <array>
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <string>
@@ -45,6 +46,17 @@ struct B200Round {
     static B200Round r;
     return r;
   }
+};
+
+// where the wall time of a round goes on this side of the C ABI (seconds, accumulated per process; read by benchmarks through
+// kcount_b200_seam_seconds): [0] staging sequences in process_seq, [1] inside the library (kc_add_* / kc_flush / kc_finish /
+// kc_copy_survivors), [2] filling the reference's local_kmers hash map from the survivor arrays
+double g_seam_seconds[3] = {0, 0, 0};
+struct SeamTimer {
+  int slot;
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  explicit SeamTimer(int s) : slot(s) {}
+  ~SeamTimer() { g_seam_seconds[slot] += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
 };
 
 void die_on(kc_handle *h, int rc, const char *what) {
@@ -86,6 +98,7 @@ static void flush_block(typename SeqBlockInserter<MAX_K>::SeqBlockInserterState 
   const uint64_t n = st->offsets.size() - 1;
   if (!n) return;
   if (!round.h) DIE("kcount_b200: process_seq before HashTableInserter::init");
+  SeamTimer tm(1);
   int rc;
   if (round.using_ctg_kmers)  // kcount_cpu.cpp:459-462: after init_ctg_kmers every supermer is a contig supermer
     rc = kc_add_contigs(round.h, st->seqs.data(), st->offsets.data(), st->depths.data(), n);
@@ -102,11 +115,14 @@ void SeqBlockInserter<MAX_K>::process_seq(string &seq, kmer_count_t depth, dist_
   (void)kmer_dht;
   const unsigned k = Kmer<MAX_K>::get_k();
   if (seq.length() < k + 2) return;  // holds no counted k-mer (kcount_cpu.cpp:84-102 starts at 1, stops before the last)
+  SeamTimer tm(0);
   state->num_kmers += seq.length() - k - 1;
   state->seqs.insert(state->seqs.end(), seq.begin(), seq.end());
   state->offsets.push_back(state->seqs.size());
   state->depths.push_back((double)depth);  // 0 -> 1 happens in the library (kcount_cpu.cpp:75)
-  if (state->seqs.size() >= STAGE_BYTES) flush_block<MAX_K>(state);
+  if (state->seqs.size() >= STAGE_BYTES) {
+    flush_block<MAX_K>(state);
+  }
 }
 
 template <int MAX_K>
@@ -116,7 +132,10 @@ void SeqBlockInserter<MAX_K>::done_processing(dist_object<KmerDHT<MAX_K>> &kmer_
   // ranks stage different numbers of batches; every batch is one exchange round inside the library. kc_flush keeps this
   // rank taking (empty) rounds until every rank is done adding, so no rank waits in a round while a peer sits in the
   // reductions and barriers that follow (kcount.cpp:93-96, kmer_dht.cpp:227-231)
-  if (auto &round = B200Round<MAX_K>::get(); round.h) die_on(round.h, kc_flush(round.h), "kc_flush");
+  if (auto &round = B200Round<MAX_K>::get(); round.h) {
+    SeamTimer tm(1);
+    die_on(round.h, kc_flush(round.h), "kc_flush");
+  }
   auto tot_kmers = reduce_one(state->num_kmers, op_fast_add, 0).wait();
   SLOG_VERBOSE("Processed a total of ", tot_kmers, " kmers\n");  // kcount_cpu.cpp:107-112
 }
@@ -194,20 +213,30 @@ void HashTableInserter<MAX_K>::flush_inserts() {
 template <int MAX_K>
 void HashTableInserter<MAX_K>::insert_into_local_hashtable(dist_object<KmerMap<MAX_K>> &local_kmers) {
   kc_handle *h = state->h;
-  die_on(h, kc_set_dmin_thres(h, _dmin_thres), "kc_set_dmin_thres");
-  die_on(h, kc_finish(h), "kc_finish");  // collective: NCCL all-to-all of the supermers, then count + filter per shard
   uint64_t n = 0;
-  die_on(h, kc_num_survivors(h, &n), "kc_num_survivors");
   const int N_LONGS = (int)Kmer<MAX_K>::get_N_LONGS();
-  vector<uint64_t> words(n * N_LONGS);
-  vector<uint16_t> counts(n);
-  vector<char> left(n), right(n);
-  die_on(h, kc_copy_survivors(h, words.data(), counts.data(), left.data(), right.data()), "kc_copy_survivors");
-  local_kmers->reserve(n);
-  for (uint64_t i = 0; i < n; i++) {
-    Kmer<MAX_K> kmer(&words[i * N_LONGS]);  // kmer.hpp:75
-    KmerCounts kmer_counts = {.uutig_frag = nullptr, .count = counts[i], .left = left[i], .right = right[i]};
-    local_kmers->insert({kmer, kmer_counts});  // kcount_cpu.cpp:513-521
+  vector<uint64_t> words;
+  vector<uint16_t> counts;
+  vector<char> left, right;
+  {
+    SeamTimer tm(1);
+    die_on(h, kc_set_dmin_thres(h, _dmin_thres), "kc_set_dmin_thres");
+    die_on(h, kc_finish(h), "kc_finish");  // collective: NCCL all-to-all of the supermers, then count + filter per shard
+    die_on(h, kc_num_survivors(h, &n), "kc_num_survivors");
+    words.resize(n * N_LONGS);
+    counts.resize(n);
+    left.resize(n);
+    right.resize(n);
+    die_on(h, kc_copy_survivors(h, words.data(), counts.data(), left.data(), right.data()), "kc_copy_survivors");
+  }
+  {
+    SeamTimer tm(2);
+    local_kmers->reserve(n);
+    for (uint64_t i = 0; i < n; i++) {
+      Kmer<MAX_K> kmer(&words[i * N_LONGS]);  // kmer.hpp:75
+      KmerCounts kmer_counts = {.uutig_frag = nullptr, .count = counts[i], .left = left[i], .right = right[i]};
+      local_kmers->insert({kmer, kmer_counts});  // kcount_cpu.cpp:513-521
+    }
   }
   kc_stats st;
   die_on(h, kc_get_stats(h, &st), "kc_get_stats");
@@ -219,6 +248,14 @@ void HashTableInserter<MAX_K>::insert_into_local_hashtable(dist_object<KmerMap<M
   SLOG_VERBOSE("B200 kcount: ", tot_distinct, " distinct kmers, purged ", perc_str(tot_purged, tot_distinct), ", kept ", tot_surv,
                " (avg per rank ", tot_surv / rank_n(), ", max ", max_surv, "); nothing dropped (", st.table_retries,
                " partitions re-run in sub-passes)\n");  // kcount_cpu.cpp:467-487,525-527
+}
+
+// benchmarks: where a round's wall time went on this side of the ABI (see g_seam_seconds); resets the counters
+extern "C" void kcount_b200_seam_seconds(double out3[3]) {
+  for (int i = 0; i < 3; i++) {
+    out3[i] = g_seam_seconds[i];
+    g_seam_seconds[i] = 0;
+  }
 }
 
 // explicit instantiations for every MAX_K the tree is built for, as kcount_cpu.cpp:533-555 does

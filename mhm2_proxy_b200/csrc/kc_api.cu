@@ -81,7 +81,7 @@ struct kc_handle {
   bool phase_open = true;   // multi-shard: this shard has added data (or never flushed) since its last drain of exchange rounds
   int dbg_key_cap = 0;      // kc_debug_set_key_cap
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> comm_ev;  // one pair around every exchange group on s_comm (ms_comm)
-  cudaStream_t s_main = nullptr, s_copy = nullptr, s_comm = nullptr;
+  cudaStream_t s_main = nullptr, s_copy = nullptr, s_comm = nullptr, s_meta = nullptr;
   std::vector<Pending> pending;
   DevBuf d_meta, d_meta_all, d_tot, d_scan, d_scan_comm;
   u64 *h_pin = nullptr;  // pinned scratch (PIN_BYTES): [0, PIN_META) bucket totals / counters, [PIN_META, ..) exchange metadata
@@ -313,6 +313,13 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   if (m < 15) m = 15;
   if (m > 27) m = 27;
   if (m > k) m = k;  // reference asserts m <= k (kmer.cpp:346); only reachable for k < 15
+  {  // one shard: which k-mers share a supermer is internal, see KC_WIDE_M in kc_extract.cuh
+    // A/B switch. OFF by default: measured on C2 (r2_v5) the parse stage gains 3.5 ms (19.2 -> 15.7 ms at k=21) but the 2 M
+    // classes of 11-mer minimizers spread unevenly over the fine buckets, a fifth of the equal-width work items overflow
+    // their key store and are re-run (count 20.2 -> 32.5 ms). Needs work items cut by instance count first.
+    static const bool wide_ok = getenv("KC_WIDE_WINDOW") && atoi(getenv("KC_WIDE_WINDOW")) != 0;
+    if (cfg->num_shards == 1 && wide_ok && kc_wide_window_ok(k)) m = KC_WIDE_M;
+  }
   h->m = m;
   h->w = k - m + 1;
   h->geom = rec_geom(k, h->w);
@@ -325,6 +332,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   CK(cudaStreamCreateWithFlags(&h->s_main, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->s_copy, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->s_comm, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&h->s_meta, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&h->ev_fill, cudaEventDisableTiming));
   CK(cudaEventCreate(&h->ev_x0));
   CK(cudaEventCreate(&h->ev_x1));
@@ -1115,32 +1123,35 @@ extern "C" int kc_set_dmin_thres(kc_handle *h, int32_t dmin_thres) {
 
 namespace {
 
-template <int KW, bool WIDE, bool CTG, int KC>
+template <int KW, bool WIDE, bool CTG, int KC, int WC>
 int launch_count(kc_handle *h, const CountArgs &ca, size_t smem, unsigned grid) {
-  CK(cudaFuncSetAttribute(count_kernel<KW, WIDE, CTG, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  count_kernel<KW, WIDE, CTG, KC><<<grid, CNT_THREADS, smem, h->s_main>>>(ca);
+  CK(cudaFuncSetAttribute(count_kernel<KW, WIDE, CTG, KC, WC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  count_kernel<KW, WIDE, CTG, KC, WC><<<grid, CNT_THREADS, smem, h->s_main>>>(ca);
   CK(cudaGetLastError());
   return KC_OK;
 }
 
-// The reference's default k schedule (options.cpp:373: 21,33,55,77,99) and k=31 get kernels with k folded in at compile time
-// (narrow counters; kc_extract.cuh); every other k, and the rare wide re-runs, take the run-time-k kernels.
+// The reference's default k schedule (options.cpp:373: 21,33,55,77,99) and k=31 get kernels with k and the supermer window
+// folded in at compile time (narrow counters; kc_extract.cuh); every other k, and the rare wide re-runs, take the
+// run-time-k kernels.
 int dispatch_count(kc_handle *h, bool wide, bool ctg, const CountArgs &ca, size_t smem, unsigned grid) {
   static const bool fixed_ok = !(getenv("KC_FIXED_K") && atoi(getenv("KC_FIXED_K")) == 0);  // A/B switch
-#define GOK(KWv, Kv)                                                                                   \
-  if (fixed_ok && !wide && h->cfg.kmer_len == Kv)                                                      \
-    return ctg ? launch_count<KWv, false, true, Kv>(h, ca, smem, grid) : launch_count<KWv, false, false, Kv>(h, ca, smem, grid)
+#define GOKW(KWv, Kv, Wv)                                                                              \
+  if (fixed_ok && !wide && h->cfg.kmer_len == Kv && h->w == Wv)                                        \
+    return ctg ? launch_count<KWv, false, true, Kv, Wv>(h, ca, smem, grid) : launch_count<KWv, false, false, Kv, Wv>(h, ca, smem, grid)
+#define GOK(KWv, Kv) GOKW(KWv, Kv, kc_w_of(Kv))
 #define GO3(KWv)                                                                               \
-  return wide ? (ctg ? launch_count<KWv, true, true, 0>(h, ca, smem, grid) : launch_count<KWv, true, false, 0>(h, ca, smem, grid)) \
-              : (ctg ? launch_count<KWv, false, true, 0>(h, ca, smem, grid) : launch_count<KWv, false, false, 0>(h, ca, smem, grid))
+  return wide ? (ctg ? launch_count<KWv, true, true, 0, 0>(h, ca, smem, grid) : launch_count<KWv, true, false, 0, 0>(h, ca, smem, grid)) \
+              : (ctg ? launch_count<KWv, false, true, 0, 0>(h, ca, smem, grid) : launch_count<KWv, false, false, 0, 0>(h, ca, smem, grid))
   switch (h->KW) {
-    case 1: GOK(1, 21); GOK(1, 31); GO3(1);
+    case 1: GOK(1, 21); GOKW(1, 21, 21 - KC_WIDE_M + 1); GOK(1, 31); GO3(1);
     case 2: GOK(2, 33); GOK(2, 55); GO3(2);
     case 3: GOK(3, 77); GO3(3);
     case 4: GOK(4, 99); GO3(4);
   }
 #undef GO3
 #undef GOK
+#undef GOKW
   return fail(h, KC_ERR_INVALID, "unsupported key width %d", h->KW);
 }
 
@@ -1782,6 +1793,7 @@ extern "C" int kc_destroy(kc_handle *h) {
   if (h->s_main) cudaStreamSynchronize(h->s_main);
   if (h->s_copy) cudaStreamSynchronize(h->s_copy);
   if (h->s_comm) cudaStreamSynchronize(h->s_comm);
+  if (h->s_meta) cudaStreamSynchronize(h->s_meta);
   for (auto &b : h->blocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   for (auto &b : h->rblocks) { dev_free(b.rec); dev_free(b.d_hist); dev_free(b.d_base); }
   for (ParseSlot &sl : h->slot) {
@@ -1810,6 +1822,7 @@ extern "C" int kc_destroy(kc_handle *h) {
   if (h->s_main) cudaStreamDestroy(h->s_main);
   if (h->s_copy) cudaStreamDestroy(h->s_copy);
   if (h->s_comm) cudaStreamDestroy(h->s_comm);
+  if (h->s_meta) cudaStreamDestroy(h->s_meta);
   pin_put(h->h_pin, h->pin_bytes);
   for (auto &p : h->pending) { dev_free(p.dir); dev_free(p.rec); }
   if (h->ev_fill) cudaEventDestroy(h->ev_fill);

@@ -142,13 +142,14 @@ __device__ __forceinline__ u32 atoms_add_ret(u32 a, u32 v) {
 // 0..5 -> A C G T F X
 __device__ __forceinline__ char ext_char(u32 c) { return c < 4u ? (char)((0x54474341u >> (8u * c)) & 0xFFu) : (c == 4u ? 'F' : 'X'); }
 
-// KC: k as a compile-time constant (0 = any k at run time, taken from CountArgs), see kc_extract.cuh
-template <int KW, bool WIDE, bool CTG, int KC>
+// KC: k as a compile-time constant (0 = any k at run time, taken from CountArgs), WC: the supermer window that goes with it
+// (kc_extract.cuh)
+template <int KW, bool WIDE, bool CTG, int KC, int WC>
 __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a) {
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int k = KC ? KC : a.k, rw = KC ? kc_rw_of(KC ? KC : 21) : a.rw;
+  const int k = KC ? KC : a.k, rw = KC ? kc_rw_of(KC, WC) : a.rw;
   const int sw = stage_words(rw);
   u32 *stage_all = (u32 *)smem_raw;                        // [CNT_GROUPS][sw], 16-byte aligned rows (sw % 4 == 0)
   u32 *tab = stage_all + CNT_GROUPS * sw;                  // [tab_size], 16-byte buckets
@@ -169,8 +170,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const u32 tab_s = (u32)__cvta_generic_to_shared(tab), keys_s = (u32)__cvta_generic_to_shared(keys),
             vals_s = (u32)__cvta_generic_to_shared(vals), stage_s = (u32)__cvta_generic_to_shared(stage),
             expl_s = (u32)__cvta_generic_to_shared(expl);
-  const int nwb = KC ? kc_nwb_of(KC ? KC : 21) : a.nwb;
-  const int w_ = KC ? kc_w_of(KC ? KC : 21) : a.w;
+  const int nwb = KC ? kc_nwb_of(KC, WC) : a.nwb;
+  const int w_ = KC ? WC : a.w;
   // supermers staged per chunk: what the staging buffer holds, and no more than the instance list will take (a supermer has
   // (w + 1) / 2 k-mers on average; staging records that do not fit the list means staging them again)
   const int sup_per_chunk = min(min(GRP_THREADS, GRP_STAGE_MAX / rw), 2 * GRP_EXP / (w_ + 1) + 3);
@@ -390,7 +391,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             if (KC) {
               const u32 rec_s = stage_s + si * (u32)(rw * 4);
               if (CTG) hdr = lds32(rec_s);
-              in = extract_fixed<KW, KC ? KC : 21>(rec_s, j, key);
+              in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
             } else {
               const u32 *rec = stage + si * rw;
               if (CTG) hdr = rec[0];
@@ -437,7 +438,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             if (KC) {
               const u32 rec_s = stage_s + si * (u32)(rw * 4);
               if (CTG) hdr = lds32(rec_s);
-              in = extract_fixed<KW, KC ? KC : 21>(rec_s, j, key);
+              in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
             } else {
               const u32 *rec = stage + si * rw;
               if (CTG) hdr = rec[0];
@@ -646,22 +647,57 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
 struct BuildArgs {
   const BlockDesc *blocks;
   u32 nblk, P;   // P = buckets of this shard (the granularity the parse stage bucketed at)
-  u32 nitems;    // item q covers buckets [q * step, min(q * step + g, P)): step == g merges neighbours (their records are
-  u32 g, step;   //   contiguous inside every batch); step > g samples the partition space (probe run)
+  u32 nitems;
+  // mode A (cum == nullptr): item q covers buckets [q * step, min(q * step + g, P)); step > g samples the bucket space (probe 1)
+  u32 g, step;
+  // mode B: items are cut by INSTANCE count, so that uneven buckets still give even items: item q covers the buckets whose
+  // first instance, in the running total over all buckets, falls in [q' * T, (q' + 1) * T), q' = q * qstride (qstride > 1
+  // samples the items: probe 2). Neighbouring buckets are contiguous inside every batch, so an item is still one segment per
+  // batch.
+  const u64 *cum;  // [P + 1] exclusive running total of the buckets' instances (all batches)
+  u64 T;
+  u32 qstride;
   int rw;
   u64 heavy_thr;  // nsup above this -> heavy
-  SegDesc *segs;  // [P * nblk]
-  WorkItem *items;  // [P]
-  u64 *heavy;     // [P]
+  SegDesc *segs;  // [(P + 2) * nblk]
+  WorkItem *items;  // [P + 2]
+  u64 *heavy;     // [P + 2]
   u64 *counters;
 };
+
+// instances of every bucket summed over the batches (clamped to 32 bits: only the balance of the cuts depends on it)
+__global__ void __launch_bounds__(256) bucket_inst_kernel(const BlockDesc *blocks, u32 nblk, u32 P, BucketHist *out) {
+  const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= P) return;
+  u64 t = 0;
+  for (u32 j = 0; j < nblk; j++) t += blocks[j].hist[blocks[j].first + b].ninst;
+  out[b].nsup = (u32)min(t, (u64)0xFFFFFFFFull);
+  out[b].ninst = 0;
+}
+
+__device__ __forceinline__ u32 first_bucket_at(const u64 *cum, u32 P, u64 x) {  // first b in [0, P] with cum[b] >= x
+  u32 lo = 0, hi = P;
+  while (lo < hi) {
+    const u32 mid = (lo + hi) >> 1;
+    if (cum[mid] >= x) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
 
 __global__ void __launch_bounds__(256) build_items_kernel(const BuildArgs a) {
   const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
   u64 nsup = 0, ri = 0, ci = 0;
   if (p < a.nitems) {
     const u32 s0 = p * a.nblk;
-    const u32 b_lo = p * a.step, b_hi = min(b_lo + a.g, a.P);
+    u32 b_lo, b_hi;
+    if (a.cum) {
+      const u64 q = (u64)p * a.qstride;
+      b_lo = first_bucket_at(a.cum, a.P, q * a.T);
+      b_hi = first_bucket_at(a.cum, a.P, (q + 1) * a.T);
+    } else {
+      b_lo = min(p * a.step, a.P);
+      b_hi = min(b_lo + a.g, a.P);
+    }
     u32 cnt = 0;
     for (u32 j = 0; j < a.nblk; j++) {
       const BlockDesc d = a.blocks[j];

@@ -21,13 +21,19 @@ __host__ __device__ constexpr int kc_m_of(int k) {
   return m > k ? k : m;
 }
 __host__ __device__ constexpr int kc_w_of(int k) { return k - kc_m_of(k) + 1; }
-__host__ __device__ constexpr int kc_nbmax_of(int k) { return kc_w_of(k) + k + 1; }
-__host__ __device__ constexpr int kc_nwb_of(int k) { return (kc_nbmax_of(k) + 15) >> 4; }
-__host__ __device__ constexpr int kc_nwv_of(int k) { return (kc_nbmax_of(k) + 31) >> 5; }
-__host__ __device__ constexpr int kc_rw_of(int k) {
-  const int need = 1 + kc_nwb_of(k) + kc_nwv_of(k);
+// record geometry for k-mer length k and supermer window w (at most w k-mers per supermer)
+__host__ __device__ constexpr int kc_nbmax_of(int k, int w) { return w + k + 1; }
+__host__ __device__ constexpr int kc_nwb_of(int k, int w) { return (kc_nbmax_of(k, w) + 15) >> 4; }
+__host__ __device__ constexpr int kc_nwv_of(int k, int w) { return (kc_nbmax_of(k, w) + 31) >> 5; }
+__host__ __device__ constexpr int kc_rw_of(int k, int w) {
+  const int need = 1 + kc_nwb_of(k, w) + kc_nwv_of(k, w);
   return need <= 4 ? 4 : (need + 7) & ~7;
 }
+// One shard, k <= 21 (16-byte records): the partition key is internal there, so supermers are cut by the minimizer of a
+// SHORTER m-mer (m = 11: window of k - 10 positions instead of k - 14): ~40 % fewer records, all of them whole 32-byte sectors
+// (kc_api.cu kc_create; with several shards the owner function fixes m, kmer_dht.cpp:113-116,192-196).
+constexpr int KC_WIDE_M = 11;
+__host__ __device__ constexpr bool kc_wide_window_ok(int k) { return k >= 17 && k <= 21; }
 
 __device__ __forceinline__ u32 lds32(u32 a) {  // a: shared-space address
   u32 v;
@@ -56,10 +62,11 @@ struct Instance {  // what the table needs to know about one k-mer instance
   u32 l, r;        // slots 0..4
 };
 
-// k known at compile time. rec_s: shared address of the staged record, j: 1-based k-mer index inside the supermer.
-template <int KW, int K>
+// k and the supermer window known at compile time. rec_s: shared address of the staged record, j: 1-based k-mer index inside
+// the supermer.
+template <int KW, int K, int W_>
 __device__ __forceinline__ Instance extract_fixed(u32 rec_s, int j, u64 (&key)[KW]) {
-  constexpr int NWB = kc_nwb_of(K);
+  constexpr int NWB = kc_nwb_of(K, W_);
   constexpr int NS = (K + 2 + 15) / 16;     // 32-bit words that hold bases j-1 .. j+k once aligned
   constexpr int NWL = (K + 17 + 15) / 16;   // words to load: the same bases at the worst alignment
   constexpr int N32 = (K + 15) / 16;        // 32-bit words of the k-mer itself
@@ -105,7 +112,6 @@ __device__ __forceinline__ Instance extract_fixed(u32 rec_s, int j, u64 (&key)[K
 #pragma unroll
   for (int i = 0; i < KW; i++) key[i] = use_rc ? rc[i] : fwd[i];
   // extension-valid bits (LSB first) follow the base words: bit j-1 for the left neighbour, bit j+k for the right one
-  constexpr int W_ = kc_w_of(K);
   const u32 va = rec_s + 4u * (1 + NWB);
   u32 lval, rval;
   if (W_ <= 32) lval = (lds32(va) >> q) & 1u;  // j-1 <= w-1 < 32: always the first word

@@ -151,9 +151,14 @@ void *odrop_run(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, co
   return res;
 }
 // timing of the seam at bench size: analyze_kmers only, the table stays in local_kmers (no sorted copy); returns seconds
+extern "C" void kcount_b200_seam_seconds(double out3[3]);
+// split of the last odrop_time: seconds staging in process_seq / inside libkcount_b200 / filling local_kmers
+void odrop_seam_seconds(double out3[3]) { kcount_b200_seam_seconds(out3); }
 double odrop_time(int k, int qual_offset, int dmin_thres, const uint8_t *bytes, const uint64_t *offs, uint64_t n_reads,
                   uint64_t *n_local_kmers) {
   Result res;
+  double scrap[3];
+  kcount_b200_seam_seconds(scrap);  // reset
   int rc = -1;
   switch ((k / 32 + 1) * 32) {
     case 32: rc = run<32>(k, qual_offset, dmin_thres, bytes, offs, n_reads, nullptr, nullptr, nullptr, 0, &res, false); break;

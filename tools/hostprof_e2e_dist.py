@@ -70,7 +70,7 @@ del hb, hb2, db, db2
 # ---- 2. phases of the e2e step ----
 uid = share_unique_id(rank, kcount.KmerCounter.comm_unique_id) if world > 1 else None
 wl = bench.Workload("C2", world, rank, reads=n)
-hout = bench.HostOut(wl.n_reads, 2)
+hout = bench.HostOut(wl.n_reads * 6, 2)
 for rep in range(4):
     barrier()
     t0 = time.perf_counter()
