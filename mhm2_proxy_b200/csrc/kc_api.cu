@@ -323,6 +323,10 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   h->m = m;
   h->w = k - m + 1;
   h->geom = rec_geom(k, h->w);
+  {  // A/B switch: pad the 16-byte records of k <= 21 to whole 32-byte sectors (one shard only: the bytes would double on the wire)
+    static const int min_rw = getenv("KC_REC_MIN_WORDS") ? atoi(getenv("KC_REC_MIN_WORDS")) : 0;
+    if (cfg->num_shards == 1 && min_rw == 8 && h->geom.rw < 8) h->geom.rw = 8;
+  }
   int ndev = 0;
   CK(cudaGetDeviceCount(&ndev));
   if (cfg->device < 0 || cfg->device >= ndev) return fail(h, KC_ERR_INVALID, "device %d of %d", cfg->device, ndev);
@@ -1269,6 +1273,8 @@ int finish_count(kc_handle *h, HostSink *sink) {
   CK(cudaMemsetAsync(d_status.p, 0, (size_t)P * sizeof(ItemStatus), h->s_main));
   u64 *ctr = h->h_pin;  // pinned
   BuildArgs ba;
+  memset(&ba, 0, sizeof(ba));  // mode A (equal-width items) unless cum is set
+  ba.qstride = 1;
   ba.blocks = (const BlockDesc *)d_descs.p;
   ba.nblk = nblk;
   ba.P = P;

@@ -149,7 +149,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int k = KC ? KC : a.k, rw = KC ? kc_rw_of(KC, WC) : a.rw;
+  const int k = KC ? KC : a.k;
+  const int rw = a.rw;  // run-time: the host may pad 16-byte records to whole sectors (kc_create)
   const int sw = stage_words(rw);
   u32 *stage_all = (u32 *)smem_raw;                        // [CNT_GROUPS][sw], 16-byte aligned rows (sw % 4 == 0)
   u32 *tab = stage_all + CNT_GROUPS * sw;                  // [tab_size], 16-byte buckets
@@ -172,6 +173,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
             expl_s = (u32)__cvta_generic_to_shared(expl);
   const int nwb = KC ? kc_nwb_of(KC, WC) : a.nwb;
   const int w_ = KC ? WC : a.w;
+  const int ncopy = (1 + nwb + ((w_ + k + 1 + 31) >> 5) + 3) >> 2;  // 16-byte pieces of a record that hold data (the rest is padding)
   // supermers staged per chunk: what the staging buffer holds, and no more than the instance list will take (a supermer has
   // (w + 1) / 2 k-mers on average; staging records that do not fit the list means staging them again)
   const int sup_per_chunk = min(min(GRP_THREADS, GRP_STAGE_MAX / rw), 2 * GRP_EXP / (w_ + 1) + 3);
@@ -256,7 +258,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           nk = (v.x & 0xFFFFu) - (u32)k - 1u;
           if (CTG) v.x |= segc[si].is_ctg << 15;  // nb <= 256: bit 15 of the header is free
           dst[0] = v;
-          for (int x = 1; x < (rw >> 2); x++) dst[x] = __ldg(src + x);
+          for (int x = 1; x < ncopy; x++) dst[x] = __ldg(src + x);
         }
         // ---- b. scan of the k-mer counts inside the pipeline; how many supermers fit this chunk ----
         u32 ik = nk;

@@ -7,10 +7,10 @@ set -u
 TAG=${1:-vX}
 OUT=gpurun_out
 mkdir -p $OUT
-python bench.py --steps 3 --warmup 3 > $OUT/${TAG}_bench_n1.json 2> $OUT/${TAG}_bench_n1.err || exit 1
+python bench.py --steps ${STEPS:-10} --warmup 3 ${BENCH_EXTRA:-} > $OUT/${TAG}_bench_n1.json 2> $OUT/${TAG}_bench_n1.err || exit 1
 tail -c 600 $OUT/${TAG}_bench_n1.json
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_launches.csv \
-  python bench.py --steps 3 --warmup 3 > $OUT/${TAG}_ncu_bench.log 2>&1
+  python bench.py --steps 3 --warmup 3 --parity off --no-cpu --e2e-steps 1 > $OUT/${TAG}_ncu_bench.log 2>&1
 echo "launch list rc=$?"
 python tools/prof_run.py 13333334 21,33 > $OUT/${TAG}_prof_run.log 2>&1 || exit 1
 timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'count_kernel|parse_kernel|fill_kernel' \
