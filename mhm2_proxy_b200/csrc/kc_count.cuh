@@ -40,6 +40,19 @@ constexpr int GRP_EXP = 160;           // k-mer instances per pipeline and chunk
 static_assert(GRP_THREADS == 32, "a pipeline is one warp");
 __host__ __device__ inline int stage_words(int rw) { return (32 * rw < GRP_STAGE_MAX ? 32 * rw : GRP_STAGE_MAX) + 4; }
 constexpr int SEG_CACHE = 64;          // segment descriptors cached per round
+// Miss queue (keys of <= 2 words): an instance whose k-mer is not where the one-load lookup expects it (new key, key in a
+// neighbouring bucket, shared fingerprint) parks its KEY and counter slots in a per-warp ring and goes on; whenever 32 are
+// waiting, the warp runs them through find-or-claim with every lane busy. (Until r2_v6 the instance's list entry was kept and
+// the k-mer extracted again at the end of its chunk: ncu showed that pass at 12 of 32 lanes and the second extraction as 9 %
+// of all instructions.)
+#ifndef KC_MISS_QUEUE
+#define KC_MISS_QUEUE 1
+#endif
+constexpr int QCAP = 64;               // ring entries per warp: < 32 waiting + up to 32 new ones
+__host__ __device__ constexpr bool miss_queue_on(int KW) { return KC_MISS_QUEUE && KW <= 2; }
+__host__ __device__ constexpr size_t miss_queue_bytes(int KW, bool ctg) {  // all warps of the CTA
+  return miss_queue_on(KW) ? (size_t)CNT_GROUPS * QCAP * ((size_t)KW * 8 + (ctg ? 4 : 1)) : 0;
+}
 constexpr u32 IDX_BITS = 13, IDX_MASK = (1u << IDX_BITS) - 1u;  // dense index + 1 fits 13 bits: key_cap <= 8190
 constexpr int VR_NARROW = 5, VR_WIDE = 9, V_CTG = 3;
 
@@ -112,7 +125,9 @@ struct CountArgs {
 // dynamic shared memory of the count kernel: per-warp staging buffers (first: their addresses are cheap to derive), index
 // table, dense key store, counters. The instance lists and the segment cache are static arrays (COUNT_STATIC_SMEM).
 __host__ __device__ inline size_t count_smem_bytes(int KW, int VW, int rw, u32 tab_size, u32 key_cap) {
-  return (size_t)CNT_GROUPS * stage_words(rw) * 4 + (size_t)tab_size * 4 + (size_t)key_cap * (KW * 8 + VW * 4) + 8;
+  const bool ctg = VW == VR_NARROW + V_CTG || VW == VR_WIDE + V_CTG;
+  return (size_t)CNT_GROUPS * stage_words(rw) * 4 + miss_queue_bytes(KW, ctg) + (size_t)tab_size * 4 +
+         (size_t)key_cap * (KW * 8 + VW * 4) + 8;
 }
 constexpr size_t COUNT_STATIC_SMEM = 13 * 1024;  // >= the kernel's static arrays (ptxas -v: 12.1 KB)
 
@@ -125,6 +140,25 @@ __device__ __forceinline__ uint4 lds128_volatile(u32 a) {  // a: shared-space ad
 __device__ __forceinline__ u64 lds64_volatile(u32 a) {
   u64 v;
   asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts64(u32 a, u64 v) {
+  asm volatile("st.shared.u64 [%0], %1;" ::"r"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ void sts32(u32 a, u32 v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts8(u32 a, u32 v) {
+  asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ u32 lds8_volatile(u32 a) {
+  u32 v;
+  asm volatile("ld.volatile.shared.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ u32 lds32_volatile(u32 a) {
+  u32 v;
+  asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
   return v;
 }
 __device__ __forceinline__ void sts16(u32 a, u32 v) {
@@ -152,8 +186,11 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const int k = KC ? KC : a.k;
   const int rw = a.rw;  // run-time: the host may pad 16-byte records to whole sectors (kc_create)
   const int sw = stage_words(rw);
+  constexpr bool QUEUE = miss_queue_on(KW);
+  constexpr u32 QMB = CTG ? 4u : 1u;                       // bytes of a queued instance's counter slots (+ contig header bits)
   u32 *stage_all = (u32 *)smem_raw;                        // [CNT_GROUPS][sw], 16-byte aligned rows (sw % 4 == 0)
-  u32 *tab = stage_all + CNT_GROUPS * sw;                  // [tab_size], 16-byte buckets
+  unsigned char *mq_all = (unsigned char *)(stage_all + CNT_GROUPS * sw);  // miss queues: keys [CNT_GROUPS][QCAP][KW], then slots
+  u32 *tab = (u32 *)(mq_all + miss_queue_bytes(KW, CTG));  // [tab_size], 16-byte buckets
   u64 *keys = (u64 *)(tab + a.tab_size);                   // [key_cap * KW]
   u32 *vals = (u32 *)(keys + (size_t)a.key_cap * KW);      // [key_cap * VW]
   __shared__ uint16_t expl_all[CNT_GROUPS][GRP_EXP];
@@ -171,6 +208,8 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
   const u32 tab_s = (u32)__cvta_generic_to_shared(tab), keys_s = (u32)__cvta_generic_to_shared(keys),
             vals_s = (u32)__cvta_generic_to_shared(vals), stage_s = (u32)__cvta_generic_to_shared(stage),
             expl_s = (u32)__cvta_generic_to_shared(expl);
+  const u32 mqk_s = (u32)__cvta_generic_to_shared(mq_all) + (u32)grp * (u32)(QCAP * KW * 8);
+  const u32 mqm_s = (u32)__cvta_generic_to_shared(mq_all) + (u32)(CNT_GROUPS * QCAP * KW * 8) + (u32)grp * (u32)QCAP * QMB;
   const int nwb = KC ? kc_nwb_of(KC, WC) : a.nwb;
   const int w_ = KC ? WC : a.w;
   const int ncopy = (1 + nwb + ((w_ + k + 1 + 31) >> 5) + 3) >> 2;  // 16-byte pieces of a record that hold data (the rest is padding)
@@ -229,6 +268,119 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
     const bool may_wrap = it.ninst >= 65536u;
     u32 spare = 0xFFFFFFFFu;  // a dense entry this thread reserved but could not publish (same key claimed concurrently)
 
+    // counters of dense entry idx: meta = left slot | right slot << 3 | (contigs) header bits 15..31
+    auto update = [&](u32 idx, u32 meta) {
+      const u32 sl = meta & 7u, sr = (meta >> 3) & 7u;
+      const u32 va = vals_s + idx * (u32)(VW * 4);
+      if (!CTG || !(meta & 0x8000u)) {  // a read instance (count 1: kcount_cpu.cpp:75,348-352)
+        if (WIDE) {
+          atoms_add(va + 4u * sl, 1u);
+          if (sr < 4u) atoms_add(va + 4u * (5u + sr), 1u);
+        } else {
+          // u16 halves: left slots 0..4 are halves 0..4, right slots 0..4 halves 5..9 (half 9 = right "none": a spare that
+          // is never read, so the right add needs no predicate). A half that was 0xFFFF before the add has wrapped (into
+          // its neighbour): the item is re-run with wide counters. Items of < 65536 instances cannot wrap: no check.
+          const u32 hl = sl, hr = 5u + sr;
+          const u32 il = 1u + (hl & 1u) * 0xFFFFu, ir = 1u + (hr & 1u) * 0xFFFFu;
+          if (may_wrap) {
+            u32 old = atoms_add_ret(va + ((hl << 1) & ~3u), il);
+            if ((old | ((hl & 1u) ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
+            if (sr < 4u) {
+              old = atoms_add_ret(va + ((hr << 1) & ~3u), ir);
+              if ((old | ((hr & 1u) ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
+            }
+          } else {
+            atoms_add(va + ((hl << 1) & ~3u), il);
+            atoms_add(va + ((hr << 1) & ~3u), ir);
+          }
+        }
+      } else {  // a contig instance: remembered as (occurrences, min depth, set of extension pairs), DESIGN.md "contig pass"
+        u32 *v = vals + (size_t)idx * VW;
+        atomicAdd(v + VR, 1u);
+        atomicMax(v + VR + 1, ~(meta >> 16));
+        atomicOr(v + VR + 2, 1u << (sl * 5 + sr));
+      }
+    };
+    // probe and claim: returns the key's dense entry, or 0xFFFFFFFF when the key store is full (the item is re-run)
+    auto find_or_claim = [&](const u64 (&key)[KW]) -> u32 {
+      const u64 h = table_hash<KW>(key);
+      const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
+      u32 bkt = __umulhi((u32)h, nbuckets);
+      u32 idx = 0xFFFFFFFFu, mine = 0xFFFFFFFFu, probes = 0;
+      bool claimed = false;
+      for (;;) {
+        const uint4 bq = lds128_volatile(tab_s + 16u * bkt);
+        const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
+        if (mn <= IDX_MASK) {  // some entry carries our fingerprint: almost always the key itself (claimed meanwhile)
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const u32 eq = q == 0 ? bq.x : q == 1 ? bq.y : q == 2 ? bq.z : bq.w;
+            if ((eq ^ fp) <= IDX_MASK && idx == 0xFFFFFFFFu) {
+              const u32 c2 = (eq & IDX_MASK) - 1u;
+              bool s2 = true;
+#pragma unroll
+              for (int i = 0; i < KW; i++) s2 = s2 && (lds64_volatile(keys_s + c2 * (u32)(KW * 8) + 8u * i) == key[i]);
+              if (s2) idx = c2;
+            }
+          }
+          if (idx != 0xFFFFFFFFu) break;
+        }
+        // entries of a bucket are claimed in order and never removed, so the occupied ones are a prefix: the bucket has
+        // room iff its last entry is empty, and the first empty entry is the number of occupied ones (a stale view can
+        // only point at an entry that is already taken: the CAS fails and the bucket is read again)
+        if (bq.w == 0u) {  // the key is not in the table: claim the bucket's first empty entry
+          if (mine == 0xFFFFFFFFu) {  // reserve a dense entry (or reuse the one a lost race left us), fill it, publish it
+            if (spare != 0xFFFFFFFFu) {
+              mine = spare;
+              spare = 0xFFFFFFFFu;
+            } else {
+              mine = atomicAdd(&s_nkeys, 1u);
+              if (mine >= a.key_cap) {
+                s_over = 1;
+                break;
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
+            __threadfence_block();
+          }
+          const u32 q = (bq.x != 0u ? 1u : 0u) + (bq.y != 0u ? 1u : 0u) + (bq.z != 0u ? 1u : 0u);
+          if (atomicCAS(&tab[4 * bkt + q], 0u, fp | (mine + 1u)) == 0u) {
+            idx = mine;
+            claimed = true;
+            break;
+          }
+          // somebody else took that entry: look at this bucket again (it may now hold our key)
+        } else {
+          probes++;
+          bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
+        }
+      }
+      if (mine != 0xFFFFFFFFu && !claimed && mine < a.key_cap) {  // lost a same-key race: the entry stays ours for the next new key
+        keys[(size_t)mine * KW + KW - 1] = KEY_EMPTY;
+        spare = mine;
+      }
+      my_max_probe = max(my_max_probe, probes);
+      return idx;
+    };
+    // miss queue of this warp (QUEUE): ring positions [qh, qh + qn) hold instances waiting for find-or-claim
+    u32 qh = 0, qn = 0;
+    auto drain = [&](u32 n) {  // the n <= 32 oldest waiting instances, one per lane
+      __syncwarp();            // the entries were written by other lanes
+      if ((u32)gt < n) {
+        const u32 pos = (qh + (u32)gt) & (u32)(QCAP - 1);
+        u64 key[KW];
+#pragma unroll
+        for (int i = 0; i < KW; i++) key[i] = lds64_volatile(mqk_s + pos * (u32)(KW * 8) + 8u * i);
+        const u32 meta = CTG ? lds32_volatile(mqm_s + pos * QMB) : lds8_volatile(mqm_s + pos * QMB);
+        const u32 idx = find_or_claim(key);
+        if (idx != 0xFFFFFFFFu) update(idx, meta);
+      }
+      qh = (qh + n) & (u32)(QCAP - 1);
+      qn -= n;
+      __syncwarp();            // entries are free for the next pushes only once every lane has read its own
+    };
+
     for (u32 sg0 = 0; sg0 < nseg; sg0 += SEG_CACHE) {
       const int ns = (int)min((u32)SEG_CACHE, nseg - sg0);
       __syncthreads();
@@ -244,19 +396,34 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
       int seg_hint = 0;
       while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
       u32 consumed = 0;
-      while (c0 < g_hi) {
-        // ---- a. one supermer record per thread: copy it to the staging buffer ----
-        const u32 g = c0 + (u32)gt;
-        const bool have = gt < sup_per_chunk && g < g_hi;
-        u32 nk = 0;
-        if (have) {
+      // The record a lane stages is requested one chunk ahead (its first 16 bytes: header + first bases; the rest of the
+      // record shares its sector): ncu r2_v7 showed 7.5 % of all warp samples waiting for this load at the top of a chunk.
+      const uint4 *nsrc = nullptr;
+      uint4 nv = make_uint4(0, 0, 0, 0);
+      u32 nctg = 0;
+      auto fetch = [&](u32 g) {
+        nsrc = nullptr;
+        if (gt < sup_per_chunk && g < g_hi) {
           int si = seg_hint;
           while (si + 1 < ns && segc[si + 1].sup0 <= g) si++;
-          const uint4 *src = (const uint4 *)(segc[si].rec + (size_t)(g - segc[si].sup0) * rw);
+          nsrc = (const uint4 *)(segc[si].rec + (size_t)(g - segc[si].sup0) * rw);
+          nv = __ldg(nsrc);
+          if (CTG) nctg = segc[si].is_ctg << 15;  // nb <= 256: bit 15 of the header is free
+        }
+      };
+      constexpr bool PREFETCH = KW == 1;  // measured (r2_v8): k=21 count 19.3 -> 18.8 ms; k=33 (64 registers) 23.7 -> 24.2 ms
+      if (PREFETCH) fetch(c0 + (u32)gt);
+      while (c0 < g_hi) {
+        // ---- a. one supermer record per thread: copy it to the staging buffer ----
+        if (!PREFETCH) fetch(c0 + (u32)gt);
+        const uint4 *src = nsrc;
+        const bool have = src != nullptr;
+        u32 nk = 0;
+        if (have) {
           uint4 *dst = (uint4 *)(stage + gt * rw);
-          uint4 v = __ldg(src);
+          uint4 v = nv;
           nk = (v.x & 0xFFFFu) - (u32)k - 1u;
-          if (CTG) v.x |= segc[si].is_ctg << 15;  // nb <= 256: bit 15 of the header is free
+          if (CTG) v.x |= nctg;
           dst[0] = v;
           for (int x = 1; x < ncopy; x++) dst[x] = __ldg(src + x);
         }
@@ -267,110 +434,32 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
           const u32 y = __shfl_up_sync(0xffffffffu, ik, d);
           if (lane >= d) ik += y;
         }
-        const bool fits = have && ik <= (u32)GRP_EXP;  // prefix sums are monotone: the fitting ones are a prefix
-        const u32 n_take = (u32)__popc(__ballot_sync(0xffffffffu, fits));
+        const bool fits0 = have && ik <= (u32)GRP_EXP;  // prefix sums are monotone: the fitting ones are a prefix
+        u32 n_take = (u32)__popc(__ballot_sync(0xffffffffu, fits0));
+        // The instances are consumed 32 at a time: a chunk whose total is just above a multiple of 32 runs its last iteration
+        // almost empty (ncu r2_v6: 28.2 of 32 lanes on the fast path). Unless this is the last chunk of the warp's range, give
+        // up to 8 supermers back to the next chunk when that leaves a total that fills its last iteration (<= 5 idle lanes).
+        {
+          const u32 rem = ik & 31u;
+          u32 gm = __ballot_sync(0xffffffffu, fits0 && (rem == 0u || rem >= 27u));
+          if (n_take > 9u) gm &= ~((1u << (n_take - 9u)) - 1u);
+          if (gm && c0 + n_take < g_hi) n_take = 32u - (u32)__clz(gm);
+        }
+        const bool fits = have && (u32)gt < n_take;
         const u32 total = __reduce_add_sync(0xffffffffu, fits ? nk : 0u);
+        if (PREFETCH) fetch(c0 + n_take + (u32)gt);  // the next chunk's records travel while this chunk's instances are counted
         if (fits) {
           const u32 koff = ik - nk;
-          for (u32 j = 0; j < nk; j++) expl[koff + j] = (uint16_t)((u32)gt | (j << 8));
+          if (KC && WC <= 12) {
+#pragma unroll
+            for (u32 j = 0; j < (u32)(KC ? WC : 1); j++)
+              if (j < nk) sts16(expl_s + 2u * (koff + j), (u32)gt | (j << 8));
+          } else {
+            for (u32 j = 0; j < nk; j++) expl[koff + j] = (uint16_t)((u32)gt | (j << 8));
+          }
         }
         __syncwarp();
 
-        // counters of dense entry idx: meta = left slot | right slot << 3 | (contigs) header bits 15..31
-        auto update = [&](u32 idx, u32 meta) {
-          const u32 sl = meta & 7u, sr = (meta >> 3) & 7u;
-          const u32 va = vals_s + idx * (u32)(VW * 4);
-          if (!CTG || !(meta & 0x8000u)) {  // a read instance (count 1: kcount_cpu.cpp:75,348-352)
-            if (WIDE) {
-              atoms_add(va + 4u * sl, 1u);
-              if (sr < 4u) atoms_add(va + 4u * (5u + sr), 1u);
-            } else {
-              // u16 halves: left slots 0..4 are halves 0..4, right slots 0..4 halves 5..9 (half 9 = right "none": a spare that
-              // is never read, so the right add needs no predicate). A half that was 0xFFFF before the add has wrapped (into
-              // its neighbour): the item is re-run with wide counters. Items of < 65536 instances cannot wrap: no check.
-              const u32 hl = sl, hr = 5u + sr;
-              const u32 il = 1u + (hl & 1u) * 0xFFFFu, ir = 1u + (hr & 1u) * 0xFFFFu;
-              if (may_wrap) {
-                u32 old = atoms_add_ret(va + ((hl << 1) & ~3u), il);
-                if ((old | ((hl & 1u) ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
-                if (sr < 4u) {
-                  old = atoms_add_ret(va + ((hr << 1) & ~3u), ir);
-                  if ((old | ((hr & 1u) ? 0x0000FFFFu : 0xFFFF0000u)) == 0xFFFFFFFFu) s_wide = 1;
-                }
-              } else {
-                atoms_add(va + ((hl << 1) & ~3u), il);
-                atoms_add(va + ((hr << 1) & ~3u), ir);
-              }
-            }
-          } else {  // a contig instance: remembered as (occurrences, min depth, set of extension pairs), DESIGN.md "contig pass"
-            u32 *v = vals + (size_t)idx * VW;
-            atomicAdd(v + VR, 1u);
-            atomicMax(v + VR + 1, ~(meta >> 16));
-            atomicOr(v + VR + 2, 1u << (sl * 5 + sr));
-          }
-        };
-        // probe and claim: returns the key's dense entry, or 0xFFFFFFFF when the key store is full (the item is re-run)
-        auto find_or_claim = [&](const u64 (&key)[KW]) -> u32 {
-          const u64 h = table_hash<KW>(key);
-          const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
-          u32 bkt = __umulhi((u32)h, nbuckets);
-          u32 idx = 0xFFFFFFFFu, mine = 0xFFFFFFFFu, probes = 0;
-          bool claimed = false;
-          for (;;) {
-            const uint4 bq = lds128_volatile(tab_s + 16u * bkt);
-            const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
-            if (mn <= IDX_MASK) {  // some entry carries our fingerprint: almost always the key itself (claimed meanwhile)
-#pragma unroll
-              for (int q = 0; q < 4; q++) {
-                const u32 eq = q == 0 ? bq.x : q == 1 ? bq.y : q == 2 ? bq.z : bq.w;
-                if ((eq ^ fp) <= IDX_MASK && idx == 0xFFFFFFFFu) {
-                  const u32 c2 = (eq & IDX_MASK) - 1u;
-                  bool s2 = true;
-#pragma unroll
-                  for (int i = 0; i < KW; i++) s2 = s2 && (lds64_volatile(keys_s + c2 * (u32)(KW * 8) + 8u * i) == key[i]);
-                  if (s2) idx = c2;
-                }
-              }
-              if (idx != 0xFFFFFFFFu) break;
-            }
-            // entries of a bucket are claimed in order and never removed, so the occupied ones are a prefix: the bucket has
-            // room iff its last entry is empty, and the first empty entry is the number of occupied ones (a stale view can
-            // only point at an entry that is already taken: the CAS fails and the bucket is read again)
-            if (bq.w == 0u) {  // the key is not in the table: claim the bucket's first empty entry
-              if (mine == 0xFFFFFFFFu) {  // reserve a dense entry (or reuse the one a lost race left us), fill it, publish it
-                if (spare != 0xFFFFFFFFu) {
-                  mine = spare;
-                  spare = 0xFFFFFFFFu;
-                } else {
-                  mine = atomicAdd(&s_nkeys, 1u);
-                  if (mine >= a.key_cap) {
-                    s_over = 1;
-                    break;
-                  }
-                }
-#pragma unroll
-                for (int i = 0; i < KW; i++) keys[(size_t)mine * KW + i] = key[i];
-                __threadfence_block();
-              }
-              const u32 q = (bq.x != 0u ? 1u : 0u) + (bq.y != 0u ? 1u : 0u) + (bq.z != 0u ? 1u : 0u);
-              if (atomicCAS(&tab[4 * bkt + q], 0u, fp | (mine + 1u)) == 0u) {
-                idx = mine;
-                claimed = true;
-                break;
-              }
-              // somebody else took that entry: look at this bucket again (it may now hold our key)
-            } else {
-              probes++;
-              bkt = (bkt + 1 == nbuckets) ? 0u : bkt + 1;
-            }
-          }
-          if (mine != 0xFFFFFFFFu && !claimed && mine < a.key_cap) {  // lost a same-key race: the entry stays ours for the next new key
-            keys[(size_t)mine * KW + KW - 1] = KEY_EMPTY;
-            spare = mine;
-          }
-          my_max_probe = max(my_max_probe, probes);
-          return idx;
-        };
         // ---- c. every k-mer instance of the chunk ----
         // Pass 1, the fast path (about 5 of 6 instances at 33x coverage): extract, hash, ONE 128-bit bucket load, key compare,
         // two counter adds. An instance that misses (new key, shared fingerprint, key that lives in a neighbouring bucket)
@@ -378,76 +467,133 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         // iteration (a quarter of all instructions). Instead the instance's LIST ENTRY is compacted to the front of the list
         // (over entries already consumed), and pass 2 walks those entries with all lanes: extracting a k-mer again costs less
         // than a third of one divergent pass through the slow path. Counter updates commute, so the order is free.
-        u32 nmiss = 0;
-        for (u32 t0 = 0; t0 < total; t0 += GRP_THREADS) {
-          const u32 t = t0 + (u32)gt;
-          bool miss = false;
-          u32 e = 0;
-          if (t < total) {
-            e = lds16(expl_s + 2u * t);
-            const u32 si = e & 255u;
-            const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
+        if (QUEUE) {
+          for (u32 t0 = 0; t0 < total; t0 += GRP_THREADS) {
+            const u32 t = t0 + (u32)gt;
+            bool miss = false;
             u64 key[KW];
-            Instance in;
-            u32 hdr = 0u;
-            if (KC) {
-              const u32 rec_s = stage_s + si * (u32)(rw * 4);
-              if (CTG) hdr = lds32(rec_s);
-              in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
-            } else {
-              const u32 *rec = stage + si * rw;
-              if (CTG) hdr = rec[0];
-              in = extract_any<KW>(rec, j, k, nwb, key);
-            }
-            const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
-            if (it.nsub <= 1 || ((u32)(h >> 40) & (it.nsub - 1)) == it.sub) {
-              // find: one 128-bit load of the bucket. entry ^ fp is (dense index + 1) <= IDX_MASK exactly when the entry's upper
-              // 19 bits equal the fingerprint (fp has bit 13 set: an empty entry never matches), so the minimum over the four
-              // words IS the candidate's index + 1 — no selects
-              const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
-              const uint4 bq = lds128_volatile(tab_s + 16u * __umulhi((u32)h, nbuckets));
-              const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
-              miss = true;
-              if (mn <= IDX_MASK) {
-                const u32 ka = keys_s + (mn - 1u) * (u32)(KW * 8);
-                bool same = true;
+            u32 meta = 0u;
+            if (t < total) {
+              const u32 e = lds16(expl_s + 2u * t);
+              const u32 si = e & 255u;
+              const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
+              Instance in;
+              u32 hdr = 0u;
+              if (KC) {
+                const u32 rec_s = stage_s + si * (u32)(rw * 4);
+                if (CTG) hdr = lds32(rec_s);
+                in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
+              } else {
+                const u32 *rec = stage + si * rw;
+                if (CTG) hdr = rec[0];
+                in = extract_any<KW>(rec, j, k, nwb, key);
+              }
+              meta = in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u);
+              const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
+              if (it.nsub <= 1 || ((u32)(h >> 40) & (it.nsub - 1)) == it.sub) {
+                // find: one 128-bit load of the bucket. entry ^ fp is (dense index + 1) <= IDX_MASK exactly when the entry's upper
+                // 19 bits equal the fingerprint (fp has bit 13 set: an empty entry never matches), so the minimum over the four
+                // words IS the candidate's index + 1 — no selects
+                const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
+                const uint4 bq = lds128_volatile(tab_s + 16u * __umulhi((u32)h, nbuckets));
+                const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
+                miss = true;
+                if (mn <= IDX_MASK) {
+                  const u32 ka = keys_s + (mn - 1u) * (u32)(KW * 8);
+                  bool same = true;
 #pragma unroll
-                for (int i = 0; i < KW; i++) same = same && (lds64_volatile(ka + 8u * i) == key[i]);
-                if (same) {
-                  miss = false;
-                  update(mn - 1u, in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u));
+                  for (int i = 0; i < KW; i++) same = same && (lds64_volatile(ka + 8u * i) == key[i]);
+                  if (same) {
+                    miss = false;
+                    update(mn - 1u, meta);
+                  }
                 }
               }
             }
-          }
-          const u32 mm = __ballot_sync(0xffffffffu, miss);
-          if (mm) {  // entries [0, nmiss) are behind the read position: nmiss <= t0
-            if (miss) sts16(expl_s + 2u * (nmiss + (u32)__popc(mm & ((1u << gt) - 1u))), e);
-            nmiss += (u32)__popc(mm);
-          }
-        }
-        __syncwarp();
-        // pass 2: the misses, all lanes busy
-        for (u32 t0 = 0; t0 < nmiss; t0 += GRP_THREADS) {
-          const u32 t = t0 + (u32)gt;
-          if (t < nmiss) {
-            const u32 e = lds16(expl_s + 2u * t);
-            const u32 si = e & 255u;
-            const int j = (int)(e >> 8) + 1;
-            u64 key[KW];
-            Instance in;
-            u32 hdr = 0u;
-            if (KC) {
-              const u32 rec_s = stage_s + si * (u32)(rw * 4);
-              if (CTG) hdr = lds32(rec_s);
-              in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
-            } else {
-              const u32 *rec = stage + si * rw;
-              if (CTG) hdr = rec[0];
-              in = extract_any<KW>(rec, j, k, nwb, key);
+            const u32 mm = __ballot_sync(0xffffffffu, miss);
+            if (mm) {  // park key + slots at the ring's tail; 32 waiting -> one full-warp pass through find-or-claim
+              if (miss) {
+                const u32 pos = (qh + qn + (u32)__popc(mm & ((1u << gt) - 1u))) & (u32)(QCAP - 1);
+#pragma unroll
+                for (int i = 0; i < KW; i++) sts64(mqk_s + pos * (u32)(KW * 8) + 8u * i, key[i]);
+                if (CTG) sts32(mqm_s + pos * QMB, meta); else sts8(mqm_s + pos * QMB, meta);
+              }
+              qn += (u32)__popc(mm);
+              if (qn >= 32u) drain(32u);
             }
-            const u32 idx = find_or_claim(key);
-            if (idx != 0xFFFFFFFFu) update(idx, in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u));
+          }
+        } else {
+          u32 nmiss = 0;
+          for (u32 t0 = 0; t0 < total; t0 += GRP_THREADS) {
+            const u32 t = t0 + (u32)gt;
+            bool miss = false;
+            u32 e = 0;
+            if (t < total) {
+              e = lds16(expl_s + 2u * t);
+              const u32 si = e & 255u;
+              const int j = (int)(e >> 8) + 1;  // k-mer index inside the supermer, 1-based (kcount_cpu.cpp:319)
+              u64 key[KW];
+              Instance in;
+              u32 hdr = 0u;
+              if (KC) {
+                const u32 rec_s = stage_s + si * (u32)(rw * 4);
+                if (CTG) hdr = lds32(rec_s);
+                in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
+              } else {
+                const u32 *rec = stage + si * rw;
+                if (CTG) hdr = rec[0];
+                in = extract_any<KW>(rec, j, k, nwb, key);
+              }
+              const u64 h = table_hash<KW>(key);  // internal slot hash (kc_device.cuh); Kmer::hash is not needed for parity
+              if (it.nsub <= 1 || ((u32)(h >> 40) & (it.nsub - 1)) == it.sub) {
+                // find: one 128-bit load of the bucket. entry ^ fp is (dense index + 1) <= IDX_MASK exactly when the entry's upper
+                // 19 bits equal the fingerprint (fp has bit 13 set: an empty entry never matches), so the minimum over the four
+                // words IS the candidate's index + 1 — no selects
+                const u32 fp = ((u32)(h >> 32) & ~IDX_MASK) | (1u << IDX_BITS);
+                const uint4 bq = lds128_volatile(tab_s + 16u * __umulhi((u32)h, nbuckets));
+                const u32 mn = min(min(bq.x ^ fp, bq.y ^ fp), min(bq.z ^ fp, bq.w ^ fp));
+                miss = true;
+                if (mn <= IDX_MASK) {
+                  const u32 ka = keys_s + (mn - 1u) * (u32)(KW * 8);
+                  bool same = true;
+#pragma unroll
+                  for (int i = 0; i < KW; i++) same = same && (lds64_volatile(ka + 8u * i) == key[i]);
+                  if (same) {
+                    miss = false;
+                    update(mn - 1u, in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u));
+                  }
+                }
+              }
+            }
+            const u32 mm = __ballot_sync(0xffffffffu, miss);
+            if (mm) {  // entries [0, nmiss) are behind the read position: nmiss <= t0
+              if (miss) sts16(expl_s + 2u * (nmiss + (u32)__popc(mm & ((1u << gt) - 1u))), e);
+              nmiss += (u32)__popc(mm);
+            }
+          }
+          __syncwarp();
+          // pass 2: the misses, all lanes busy
+          for (u32 t0 = 0; t0 < nmiss; t0 += GRP_THREADS) {
+            const u32 t = t0 + (u32)gt;
+            if (t < nmiss) {
+              const u32 e = lds16(expl_s + 2u * t);
+              const u32 si = e & 255u;
+              const int j = (int)(e >> 8) + 1;
+              u64 key[KW];
+              Instance in;
+              u32 hdr = 0u;
+              if (KC) {
+                const u32 rec_s = stage_s + si * (u32)(rw * 4);
+                if (CTG) hdr = lds32(rec_s);
+                in = extract_fixed<KW, KC ? KC : 21, KC ? WC : 7>(rec_s, j, key);
+              } else {
+                const u32 *rec = stage + si * rw;
+                if (CTG) hdr = rec[0];
+                in = extract_any<KW>(rec, j, k, nwb, key);
+              }
+              const u32 idx = find_or_claim(key);
+              if (idx != 0xFFFFFFFFu) update(idx, in.l | (in.r << 3) | (CTG ? (hdr & 0xFFFF8000u) : 0u));
+            }
           }
         }
         const bool stop = __any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0);  // also orders this chunk's reads of the
@@ -458,6 +604,9 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
         while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
       }
       if (gt == 0 && consumed) atomicAdd(&s_consumed, consumed);
+    }
+    if (QUEUE) {  // what is still waiting (fewer than 32 per warp)
+      while (qn && !__any_sync(0xffffffffu, *(volatile u32 *)&s_over != 0u)) drain(min(qn, 32u));
     }
     __syncthreads();
     const bool over = s_over != 0;

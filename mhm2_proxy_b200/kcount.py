@@ -51,10 +51,11 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+    path = os.environ.get("KCOUNT_B200_LIB", LIB_PATH)  # A/B runs of differently compiled builds (tools/ab_bench.sh)
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                            "(the kcount path is CUDA only; there is no CPU fallback)")
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(path)
     vp, u64, i32 = C.c_void_p, C.c_uint64, C.c_int32
     lib.kc_config_default.argtypes = [C.POINTER(KcConfig), i32]
     lib.kc_config_default.restype = None
