@@ -360,6 +360,40 @@ def parity_check(kcount, args, rank, world, local, wl, d_b, d_o, uid, dist):
     return out
 
 
+def copy_ceiling(world, dist, mb=256):
+    """What the box gives every rank when all ranks copy at once (plain cudaMemcpyAsync from / to pinned memory): host->device,
+    device->host, and both directions together, GB/s per rank (the minimum over ranks). The end-to-end arm moves h2d + d2h bytes
+    per step through exactly this path; with N ranks on one host the figures fall (shared PCIe switches / host memory)."""
+    import torch
+    hb = torch.empty(mb << 20, dtype=torch.uint8, pin_memory=True)
+    hb2 = torch.empty(mb << 20, dtype=torch.uint8, pin_memory=True)
+    db = torch.empty(mb << 20, dtype=torch.uint8, device="cuda")
+    db2 = torch.empty(mb << 20, dtype=torch.uint8, device="cuda")
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    out = {}
+    for what in ("h2d", "d2h", "both"):
+        best = 0.0
+        for _ in range(3):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            if what in ("h2d", "both"):
+                with torch.cuda.stream(s1):
+                    db.copy_(hb, non_blocking=True)
+            if what in ("d2h", "both"):
+                with torch.cuda.stream(s2):
+                    hb2.copy_(db2, non_blocking=True)
+            torch.cuda.synchronize()
+            best = max(best, (mb << 20) / (time.perf_counter() - t0) / 1e9)  # per direction
+        if world > 1:
+            t = torch.tensor([best], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            best = float(t.item())
+        out[what + "_gbs_per_rank_per_dir"] = round(best, 1)
+    return out
+
+
 def dropin_seam(wl, ks):
     """The real seam: the reference's own analyze_kmers (kcount.cpp, unmodified) over PackedReads with
     integration/kcount_b200.cpp as its backend, timed from 'reads in PackedReads' to 'local_kmers filled'
@@ -489,11 +523,12 @@ def run_ours(args):
         return res
 
     name = args.config or default_config(world)
+    ceiling = copy_ceiling(world, dist)
     sampler = ClockSampler(local) if rank == 0 else None
     e2e_steps = max(1, args.e2e_steps)
     m = measure(name, args.steps, args.warmup, e2e_steps, max(3, min(args.warmup, 3)), args.parity != "off", sampler)
     second = None
-    if world >= 8 and name == "C3" and not args.config and not args.no_second:
+    if (world >= 8 and name == "C3" and not args.config and not args.no_second) or (args.second and name != "C2"):
         # the C2 weak-scaled line of the N = 1, 2, 4 runs, kept beside the 8-GPU config (the C3 buffers are released first)
         m["wl"].tb = m["wl"].to = None
         torch.cuda.empty_cache()
@@ -581,6 +616,10 @@ def run_ours(args):
                 "path": ("kc_add_reads per k round" if args.e2e_per_round_upload else
                          "kc_reads_create once per step (pinned host reads -> HBM, shared by the k rounds)") +
                         " + kc_add_reads_resident + kc_finish_to_host (table -> pinned host memory) per k round"},
+        "e2e_copy_ceiling": dict(ceiling, **{
+            "what": f"all {world} rank(s) copying at once, pinned memory, GB/s per rank and direction (min over ranks)",
+            "floor_ms_per_step": round(1e3 * max(h2d / (ceiling["h2d_gbs_per_rank_per_dir"] * 1e9), d2h / (ceiling["d2h_gbs_per_rank_per_dir"] * 1e9)), 2),
+            "floor_ms_note": "the larger of the step's upload and download at those rates; the copies overlap the kernels and each other only in part"}),
         "e2e_dropin": dropin,
         "gpu_launches": int(sum(s["gpu_launches"] for s in stats)),
         "parity": m["parity"],
@@ -664,6 +703,7 @@ def main():
     ap.add_argument("--parity-chunk", dest="parity_chunk", type=int, default=2_000_000)
     ap.add_argument("--dropin", action="store_true", help="also time the reference's own analyze_kmers through the binding (e2e_dropin)")
     ap.add_argument("--no-second", dest="no_second", action="store_true", help="--gpus 8 default run: skip the C2 weak-scaled second line")
+    ap.add_argument("--second", action="store_true", help="also measure the C2 weak-scaled second line (what the --gpus 8 default run does)")
     args = ap.parse_args()
     if not args.parity_distinct_frac:
         name = args.config or default_config(args.gpus)

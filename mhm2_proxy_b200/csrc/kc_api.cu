@@ -372,7 +372,9 @@ namespace {
 // shared-memory table geometry of the count stage for this handle (kc_count.cuh): how many distinct k-mers one work item holds
 void table_geometry(const kc_handle *h, bool wide, bool ctg, u32 &tab_size, u32 &key_cap) {
   const int KW = h->KW, VW = (wide ? VR_WIDE : VR_NARROW) + (ctg ? V_CTG : 0);
-  const size_t budget = (size_t)h->smem_optin - COUNT_STATIC_SMEM;  // the kernel's static arrays + alignment slack
+  // the kernel's static arrays + alignment slack; CNT_CTAS_PER_SM CTAs (each with 1 KB reserved by the system) share the SM's 228 KB
+  const size_t per_cta = CNT_CTAS_PER_SM == 1 ? (size_t)h->smem_optin : ((size_t)h->smem_optin + 1024) / CNT_CTAS_PER_SM - 1024;
+  const size_t budget = per_cta - COUNT_STATIC_SMEM;
   const size_t fixed = count_smem_bytes(KW, VW, h->geom.rw, 0, 0) + 32;
   const size_t per_key = (size_t)KW * 8 + (size_t)VW * 4 + 8;  // + two 4-byte index-table entries (load <= 0.5)
   u64 cap = budget > fixed ? (budget - fixed) / per_key : 16;
@@ -1317,7 +1319,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
       pa.dmin_thres = h->cfg.dmin_thres;
       pa.frac = 1.0 - h->cfg.dyn_min_depth;
       pa.counters = (u64 *)d_counters.p;
-      RC(dispatch_count(h, false, any_ctg, pa, smem_p, std::min<unsigned>(S, (unsigned)h->sms)));
+      RC(dispatch_count(h, false, any_ctg, pa, smem_p, std::min<unsigned>(S, (unsigned)h->sms * CNT_CTAS_PER_SM)));
       h->st.gpu_launches += 2;
       std::vector<ItemStatus> pst(S);
       CK(cudaMemcpyAsync(ctr, d_counters.p, CTR_WORDS * 8, cudaMemcpyDeviceToHost, h->s_main));
@@ -1496,7 +1498,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
           cg.heavy = nullptr;
           cg.n_heavy = 0;
         }
-        const unsigned grid = (unsigned)std::min<size_t>((size_t)cg.nitems + cg.n_heavy, (size_t)h->sms);
+        const unsigned grid = (unsigned)std::min<size_t>((size_t)cg.nitems + cg.n_heavy, (size_t)h->sms * CNT_CTAS_PER_SM);
         RC(dispatch_count(h, wide, any_ctg, cg, smem, grid));
         h->st.gpu_launches++;
         h->st.n_insert_launches++;

@@ -32,8 +32,12 @@ namespace kc {
 
 constexpr u64 KEY_EMPTY = 0xFFFFFFFFFFFFFFFFULL;  // last key word of a real k-mer is never all ones: it has >= 2 zero
                                                   // trailing bits because N_LONGS = k/32 + 1 (main.cpp:170)
-constexpr int CNT_THREADS = 1024;
-constexpr int CNT_GROUPS = 32;         // independent pipelines per CTA: every WARP is one (no barrier inside a work item's
+#ifndef KC_CNT_THREADS
+#define KC_CNT_THREADS 1024
+#endif
+constexpr int CNT_THREADS = KC_CNT_THREADS;     // threads per CTA; CNT_CTAS_PER_SM CTAs share an SM (and its shared memory)
+constexpr int CNT_CTAS_PER_SM = 1024 / CNT_THREADS;
+constexpr int CNT_GROUPS = CNT_THREADS / 32;    // independent pipelines per CTA: every WARP is one (no barrier inside a work item's
 constexpr int GRP_THREADS = CNT_THREADS / CNT_GROUPS;  // stream of supermers: __syncwarp only)
 constexpr int GRP_STAGE_MAX = 256;     // staged record words per pipeline and chunk: min(32 records, this many words) + 4
 constexpr int GRP_EXP = 160;           // k-mer instances per pipeline and chunk
@@ -49,6 +53,10 @@ constexpr int SEG_CACHE = 64;          // segment descriptors cached per round
 #define KC_MISS_QUEUE 1
 #endif
 constexpr int QCAP = 64;               // ring entries per warp: < 32 waiting + up to 32 new ones
+#ifndef KC_DRAIN_MIN
+#define KC_DRAIN_MIN 32
+#endif
+constexpr unsigned DRAIN_MIN = KC_DRAIN_MIN;  // waiting instances that trigger a pass through find-or-claim (<= 32)
 __host__ __device__ constexpr bool miss_queue_on(int KW) { return KC_MISS_QUEUE && KW <= 2; }
 __host__ __device__ constexpr size_t miss_queue_bytes(int KW, bool ctg) {  // all warps of the CTA
   return miss_queue_on(KW) ? (size_t)CNT_GROUPS * QCAP * ((size_t)KW * 8 + (ctg ? 4 : 1)) : 0;
@@ -129,7 +137,7 @@ __host__ __device__ inline size_t count_smem_bytes(int KW, int VW, int rw, u32 t
   return (size_t)CNT_GROUPS * stage_words(rw) * 4 + miss_queue_bytes(KW, ctg) + (size_t)tab_size * 4 +
          (size_t)key_cap * (KW * 8 + VW * 4) + 8;
 }
-constexpr size_t COUNT_STATIC_SMEM = 13 * 1024;  // >= the kernel's static arrays (ptxas -v: 12.1 KB)
+constexpr size_t COUNT_STATIC_SMEM = (13 * 1024) / CNT_CTAS_PER_SM + (CNT_CTAS_PER_SM > 1 ? 1536 : 0);  // >= the kernel's static arrays (ptxas -v: 12.1 KB at 1024 threads)
 
 __device__ __forceinline__ uint4 lds128_volatile(u32 a) {  // a: shared-space address (converted once per kernel)
   uint4 v;
@@ -179,7 +187,7 @@ __device__ __forceinline__ char ext_char(u32 c) { return c < 4u ? (char)((0x5447
 // KC: k as a compile-time constant (0 = any k at run time, taken from CountArgs), WC: the supermer window that goes with it
 // (kc_extract.cuh)
 template <int KW, bool WIDE, bool CTG, int KC, int WC>
-__global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a) {
+__global__ void __launch_bounds__(CNT_THREADS, CNT_CTAS_PER_SM) count_kernel(const CountArgs a) {
   constexpr int VR = WIDE ? VR_WIDE : VR_NARROW;
   constexpr int VW = VR + (CTG ? V_CTG : 0);
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -519,7 +527,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
                 if (CTG) sts32(mqm_s + pos * QMB, meta); else sts8(mqm_s + pos * QMB, meta);
               }
               qn += (u32)__popc(mm);
-              if (qn >= 32u) drain(32u);
+              if (qn >= DRAIN_MIN) drain(min(qn, 32u));
             }
           }
         } else {
@@ -719,7 +727,7 @@ __global__ void __launch_bounds__(CNT_THREADS, 1) count_kernel(const CountArgs a
     if (lane == 0) { warp_c[wid] = n_sv; warp_p[wid] = n_pf; if (n_occ) atomicAdd(&s_live, n_occ); }
     __syncthreads();
     if (wid == 0) {
-      u32 c = warp_c[lane], p = warp_p[lane];
+      u32 c = lane < CNT_GROUPS ? warp_c[lane] : 0u, p = lane < CNT_GROUPS ? warp_p[lane] : 0u;
 #pragma unroll
       for (int d = 16; d; d >>= 1) {
         c += __shfl_xor_sync(0xffffffffu, c, d);

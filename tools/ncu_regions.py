@@ -25,12 +25,13 @@ for s in sections:
     launches[-1].append(s); seen.add(s["file"])
 sel = [l for l in launches if "count_kernel" in l[0]["fn"]][occ]
 src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mhm2_proxy_b200", "csrc", "kc_count.cuh")).read().split("\n")
-MARK = [("count_kernel(const CountArgs", "item setup / scheduling"), ("---- a. one supermer record", "a. stage records"),
-        ("---- b. scan of the k-mer counts", "b. scan + instance list"), ("---- c. every k-mer instance", "c. loop control, deferral"),
-        ("auto update = ", "counters (update)"), ("auto find_or_claim = ", "slow path (find_or_claim)"),
-        ("one more (empty) iteration", "c. loop control, deferral"), ("if (t < total) {", "c. fast path: list entry, lookup, key compare"),
-        ("if (DEFER) {", "c. loop control, deferral"), ("const bool stop = __any_sync", "chunk end"),
-        ("const bool over = s_over", "item end: status, filter, compaction, output")]
+MARK = [("count_kernel(const CountArgs", "item setup / scheduling"), ("auto update = ", "counters (update)"),
+        ("auto find_or_claim = ", "slow path (find_or_claim)"), ("auto drain = ", "miss queue: drain"),
+        ("for (u32 sg0 = 0", "round setup (segment cache, ranges)"), ("auto fetch = ", "a. stage records"),
+        ("---- a. one supermer record", "a. stage records"), ("---- b. scan of the k-mer counts", "b. scan + instance list"),
+        ("---- c. every k-mer instance", "c. loop control"), ("if (t < total) {", "c. fast path: list entry, lookup, key compare"),
+        ("const u32 mm = __ballot_sync", "c. miss queue: push"), ("const bool stop = __any_sync", "chunk end"),
+        ("what is still waiting", "miss queue: drain"), ("const bool over = s_over", "item end: status, filter, compaction, output")]
 region, cur_r = {}, "helpers"
 for i, line in enumerate(src, 1):
     for pat, name in MARK:
