@@ -313,20 +313,9 @@ extern "C" int kc_create(const kc_config *cfg, kc_handle **out) {
   if (m < 15) m = 15;
   if (m > 27) m = 27;
   if (m > k) m = k;  // reference asserts m <= k (kmer.cpp:346); only reachable for k < 15
-  {  // one shard: which k-mers share a supermer is internal, see KC_WIDE_M in kc_extract.cuh
-    // A/B switch. OFF by default: measured on C2 (r2_v5) the parse stage gains 3.5 ms (19.2 -> 15.7 ms at k=21) but the 2 M
-    // classes of 11-mer minimizers spread unevenly over the fine buckets, a fifth of the equal-width work items overflow
-    // their key store and are re-run (count 20.2 -> 32.5 ms). Needs work items cut by instance count first.
-    static const bool wide_ok = getenv("KC_WIDE_WINDOW") && atoi(getenv("KC_WIDE_WINDOW")) != 0;
-    if (cfg->num_shards == 1 && wide_ok && kc_wide_window_ok(k)) m = KC_WIDE_M;
-  }
   h->m = m;
   h->w = k - m + 1;
   h->geom = rec_geom(k, h->w);
-  {  // A/B switch: pad the 16-byte records of k <= 21 to whole 32-byte sectors (one shard only: the bytes would double on the wire)
-    static const int min_rw = getenv("KC_REC_MIN_WORDS") ? atoi(getenv("KC_REC_MIN_WORDS")) : 0;
-    if (cfg->num_shards == 1 && min_rw == 8 && h->geom.rw < 8) h->geom.rw = 8;
-  }
   int ndev = 0;
   CK(cudaGetDeviceCount(&ndev));
   if (cfg->device < 0 || cfg->device >= ndev) return fail(h, KC_ERR_INVALID, "device %d of %d", cfg->device, ndev);
@@ -1150,7 +1139,7 @@ int dispatch_count(kc_handle *h, bool wide, bool ctg, const CountArgs &ca, size_
   return wide ? (ctg ? launch_count<KWv, true, true, 0, 0>(h, ca, smem, grid) : launch_count<KWv, true, false, 0, 0>(h, ca, smem, grid)) \
               : (ctg ? launch_count<KWv, false, true, 0, 0>(h, ca, smem, grid) : launch_count<KWv, false, false, 0, 0>(h, ca, smem, grid))
   switch (h->KW) {
-    case 1: GOK(1, 21); GOKW(1, 21, 21 - KC_WIDE_M + 1); GOK(1, 31); GO3(1);
+    case 1: GOK(1, 21); GOK(1, 31); GO3(1);
     case 2: GOK(2, 33); GOK(2, 55); GO3(2);
     case 3: GOK(3, 77); GO3(3);
     case 4: GOK(4, 99); GO3(4);
@@ -1275,8 +1264,7 @@ int finish_count(kc_handle *h, HostSink *sink) {
   CK(cudaMemsetAsync(d_status.p, 0, (size_t)P * sizeof(ItemStatus), h->s_main));
   u64 *ctr = h->h_pin;  // pinned
   BuildArgs ba;
-  memset(&ba, 0, sizeof(ba));  // mode A (equal-width items) unless cum is set
-  ba.qstride = 1;
+  memset(&ba, 0, sizeof(ba));
   ba.blocks = (const BlockDesc *)d_descs.p;
   ba.nblk = nblk;
   ba.P = P;

@@ -806,57 +806,22 @@ __global__ void __launch_bounds__(CNT_THREADS, CNT_CTAS_PER_SM) count_kernel(con
 struct BuildArgs {
   const BlockDesc *blocks;
   u32 nblk, P;   // P = buckets of this shard (the granularity the parse stage bucketed at)
-  u32 nitems;
-  // mode A (cum == nullptr): item q covers buckets [q * step, min(q * step + g, P)); step > g samples the bucket space (probe 1)
-  u32 g, step;
-  // mode B: items are cut by INSTANCE count, so that uneven buckets still give even items: item q covers the buckets whose
-  // first instance, in the running total over all buckets, falls in [q' * T, (q' + 1) * T), q' = q * qstride (qstride > 1
-  // samples the items: probe 2). Neighbouring buckets are contiguous inside every batch, so an item is still one segment per
-  // batch.
-  const u64 *cum;  // [P + 1] exclusive running total of the buckets' instances (all batches)
-  u64 T;
-  u32 qstride;
+  u32 nitems;    // item q covers buckets [q * step, min(q * step + g, P)): step == g merges neighbours (their records are
+  u32 g, step;   //   contiguous inside every batch); step > g samples the partition space (probe run)
   int rw;
   u64 heavy_thr;  // nsup above this -> heavy
-  SegDesc *segs;  // [(P + 2) * nblk]
-  WorkItem *items;  // [P + 2]
-  u64 *heavy;     // [P + 2]
+  SegDesc *segs;  // [P * nblk]
+  WorkItem *items;  // [P]
+  u64 *heavy;     // [P]
   u64 *counters;
 };
-
-// instances of every bucket summed over the batches (clamped to 32 bits: only the balance of the cuts depends on it)
-__global__ void __launch_bounds__(256) bucket_inst_kernel(const BlockDesc *blocks, u32 nblk, u32 P, BucketHist *out) {
-  const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= P) return;
-  u64 t = 0;
-  for (u32 j = 0; j < nblk; j++) t += blocks[j].hist[blocks[j].first + b].ninst;
-  out[b].nsup = (u32)min(t, (u64)0xFFFFFFFFull);
-  out[b].ninst = 0;
-}
-
-__device__ __forceinline__ u32 first_bucket_at(const u64 *cum, u32 P, u64 x) {  // first b in [0, P] with cum[b] >= x
-  u32 lo = 0, hi = P;
-  while (lo < hi) {
-    const u32 mid = (lo + hi) >> 1;
-    if (cum[mid] >= x) hi = mid; else lo = mid + 1;
-  }
-  return lo;
-}
 
 __global__ void __launch_bounds__(256) build_items_kernel(const BuildArgs a) {
   const u32 p = blockIdx.x * blockDim.x + threadIdx.x;
   u64 nsup = 0, ri = 0, ci = 0;
   if (p < a.nitems) {
     const u32 s0 = p * a.nblk;
-    u32 b_lo, b_hi;
-    if (a.cum) {
-      const u64 q = (u64)p * a.qstride;
-      b_lo = first_bucket_at(a.cum, a.P, q * a.T);
-      b_hi = first_bucket_at(a.cum, a.P, (q + 1) * a.T);
-    } else {
-      b_lo = min(p * a.step, a.P);
-      b_hi = min(b_lo + a.g, a.P);
-    }
+    const u32 b_lo = min(p * a.step, a.P), b_hi = min(b_lo + a.g, a.P);
     u32 cnt = 0;
     for (u32 j = 0; j < a.nblk; j++) {
       const BlockDesc d = a.blocks[j];

@@ -29,12 +29,6 @@ __host__ __device__ constexpr int kc_rw_of(int k, int w) {
   const int need = 1 + kc_nwb_of(k, w) + kc_nwv_of(k, w);
   return need <= 4 ? 4 : (need + 7) & ~7;
 }
-// One shard, k <= 21 (16-byte records): the partition key is internal there, so supermers are cut by the minimizer of a
-// SHORTER m-mer (m = 11: window of k - 10 positions instead of k - 14): ~40 % fewer records, all of them whole 32-byte sectors
-// (kc_api.cu kc_create; with several shards the owner function fixes m, kmer_dht.cpp:113-116,192-196).
-constexpr int KC_WIDE_M = 11;
-__host__ __device__ constexpr bool kc_wide_window_ok(int k) { return k >= 17 && k <= 21; }
-
 __device__ __forceinline__ u32 lds32(u32 a) {  // a: shared-space address
   u32 v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
