@@ -401,8 +401,14 @@ __global__ void __launch_bounds__(CNT_THREADS, CNT_CTAS_PER_SM) count_kernel(con
       const u32 span = r_hi - r_lo;
       const u32 g_lo = r_lo + (u32)(((u64)span * grp) / CNT_GROUPS), g_hi = r_lo + (u32)(((u64)span * (grp + 1)) / CNT_GROUPS);
       u32 c0 = g_lo;
+      // segment of the chunk's first supermer, and where the next segment starts (most lanes of most chunks need no search)
       int seg_hint = 0;
-      while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
+      u32 seg_next = 0xFFFFFFFFu;
+      auto seek = [&](u32 c) {
+        while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c) seg_hint++;
+        seg_next = seg_hint + 1 < ns ? segc[seg_hint + 1].sup0 : 0xFFFFFFFFu;
+      };
+      seek(c0);
       u32 consumed = 0;
       // The record a lane stages is requested one chunk ahead (its first 16 bytes: header + first bases; the rest of the
       // record shares its sector): ncu r2_v7 showed 7.5 % of all warp samples waiting for this load at the top of a chunk.
@@ -413,7 +419,10 @@ __global__ void __launch_bounds__(CNT_THREADS, CNT_CTAS_PER_SM) count_kernel(con
         nsrc = nullptr;
         if (gt < sup_per_chunk && g < g_hi) {
           int si = seg_hint;
-          while (si + 1 < ns && segc[si + 1].sup0 <= g) si++;
+          if (g >= seg_next) {
+            si++;
+            while (si + 1 < ns && segc[si + 1].sup0 <= g) si++;
+          }
           nsrc = (const uint4 *)(segc[si].rec + (size_t)(g - segc[si].sup0) * rw);
           nv = __ldg(nsrc);
           if (CTG) nctg = segc[si].is_ctg << 15;  // nb <= 256: bit 15 of the header is free
@@ -609,7 +618,7 @@ __global__ void __launch_bounds__(CNT_THREADS, CNT_CTAS_PER_SM) count_kernel(con
         c0 += n_take;
         consumed += n_take;
         if (stop) break;
-        while (seg_hint + 1 < ns && segc[seg_hint + 1].sup0 <= c0) seg_hint++;
+        if (c0 >= seg_next) seek(c0);
       }
       if (gt == 0 && consumed) atomicAdd(&s_consumed, consumed);
     }
