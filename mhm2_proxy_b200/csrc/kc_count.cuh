@@ -3,8 +3,9 @@
 // L2-resident global RED, i.e. 15x). Per work item (partition, sub-pass):
 //   1. 32 independent pipelines — every warp is one — each stream 1/32 of the partition's supermer records through their
 //      own staging buffer (no barrier inside a work item, only __syncwarp) and all insert into ONE table;
-//   2. records are expanded to k-mer instances, canonicalised, hashed (internal slot hash, kc_device.cuh), found or claimed, and
-//      the extension counters bumped with shared-memory atomics
+//   2. records are expanded to k-mer instances, canonicalised, hashed (internal slot hash, kc_device.cuh), looked up with ONE
+//      128-bit bucket load (instances whose key is not there yet wait in a per-warp miss queue and are found or claimed 32 at
+//      a time), and the extension counters bumped with shared-memory atomics
 //         replaces get_kmers_and_exts + KmerMapExts::insert + insert_supermer_from_read/_from_ctg
 //         (reference src/kcount/kcount_cpu.cpp:231-267,307-406);
 //   3. the dense key store is scanned: depth filter + extension choice + compaction of survivors straight to the output
@@ -478,12 +479,13 @@ __global__ void __launch_bounds__(CNT_THREADS, CNT_CTAS_PER_SM) count_kernel(con
         __syncwarp();
 
         // ---- c. every k-mer instance of the chunk ----
-        // Pass 1, the fast path (about 5 of 6 instances at 33x coverage): extract, hash, ONE 128-bit bucket load, key compare,
-        // two counter adds. An instance that misses (new key, shared fingerprint, key that lives in a neighbouring bucket)
-        // needs the probe-and-claim path; handled where it occurs that path ran with 4-8 of 32 lanes active in almost every
-        // iteration (a quarter of all instructions). Instead the instance's LIST ENTRY is compacted to the front of the list
-        // (over entries already consumed), and pass 2 walks those entries with all lanes: extracting a k-mer again costs less
-        // than a third of one divergent pass through the slow path. Counter updates commute, so the order is free.
+        // The fast path (about 4 of 5 instances at 33x coverage): extract, hash, ONE 128-bit bucket load, key compare, two
+        // counter adds. An instance that misses (new key, key still waiting in somebody's queue, shared fingerprint, key that
+        // lives in a neighbouring bucket) needs the probe-and-claim path; handled where it occurs that path ran with 4-8 of
+        // 32 lanes active in almost every iteration (a quarter of all instructions). QUEUE (keys of <= 2 words): the instance
+        // parks key + counter slots in the warp's ring and find-or-claim runs whenever 32 are waiting. Otherwise (keys of 3-4
+        // words, whose ring would cost a third of the table): its LIST ENTRY is compacted to the front of the list and a
+        // second pass extracts those k-mers again with all lanes. Counter updates commute, so the order is free.
         if (QUEUE) {
           for (u32 t0 = 0; t0 < total; t0 += GRP_THREADS) {
             const u32 t = t0 + (u32)gt;
