@@ -68,3 +68,24 @@ def test_reference_arm_prints_the_contract_line(built):
     assert d["cpu_baseline"]["kind"] == "reference" and d["cpu_baseline"]["cores"] >= 1 and "4000 reads" in d["cpu_baseline"]["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "kmers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["config"]["k"] == [21, 33] and d["config"]["workload"].startswith("C2:")
+
+
+def test_traffic_json_is_what_the_committed_ncu_pages_say(tmp_path):
+    """profiles/traffic.json (read back into roofline.traffic) must be regenerable from the committed ncu raw pages: no
+    hand-edited constants (evidence hygiene)."""
+    import shutil
+    prof = os.path.join(ROOT, "profiles")
+    cur = json.load(open(os.path.join(prof, "traffic.json")))
+    tag = cur["_comment"].split("capture ")[1].split(" ")[0]
+    raws = [os.path.join(prof, f"{tag}_count_raw.csv"), os.path.join(prof, f"{tag}_parse_raw.csv")]
+    assert all(os.path.exists(r) for r in raws), raws
+    # run the generator on a scratch copy of the tree layout (it writes <root>/profiles/traffic.json next to tools/)
+    scratch = tmp_path / "repo"
+    (scratch / "tools").mkdir(parents=True)
+    (scratch / "profiles").mkdir()
+    shutil.copy(os.path.join(ROOT, "tools", "make_traffic.py"), scratch / "tools" / "make_traffic.py")
+    out = subprocess.run([sys.executable, str(scratch / "tools" / "make_traffic.py"), tag] + raws, capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    new = json.load(open(scratch / "profiles" / "traffic.json"))
+    for k in ("count_kernel", "parse_kernel", "fill_kernel"):
+        assert new[k] == cur[k], (k, new[k], cur[k])
